@@ -1,0 +1,70 @@
+"""Build libekat_b200.so (hand-written CUDA for sm_100a + the C ABI) in-tree with nvcc.
+
+    python -m ekat_b200.build [--force] [--verbose]
+
+nvcc cross-compiles without a GPU, so this runs in the CPU-only build container; the
+resulting ekat_b200/lib/libekat_b200.so is git-ignored but travels with the repo to the
+GPU box. No torch, no JIT cache: plain `nvcc -shared`.
+"""
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIBDIR = os.path.join(HERE, "lib")
+LIB = os.path.join(LIBDIR, "libekat_b200.so")
+SOURCES = ["capi.cu", "tridiag_levmajor.cu", "tridiag_tile.cu", "lin_interp.cu", "fused.cu", "util.cu", "host_pipeline.cu"]
+HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(HERE, "..", "include", "ekat_b200", "ekat_b200.h")]
+NVCC = os.environ.get("EKAT_B200_NVCC", "nvcc")
+# sm_100a only (no PTX for other archs, no multi-arch fatbin). -lineinfo for ncu source pages.
+# No -use_fast_math / -fmad toggles: exactness is spelled with __d*_rn / __f*_rn intrinsics.
+FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-ccbin", "g++",
+         "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
+
+
+def _stale(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build(force=False, verbose=False):
+    os.makedirs(LIBDIR, exist_ok=True)
+    objs, jobs = [], []
+    for s in SOURCES:
+        src = os.path.join(CSRC, s)
+        obj = os.path.join(LIBDIR, s.replace(".cu", ".o"))
+        objs.append(obj)
+        if force or _stale(obj, [src] + HEADERS):
+            jobs.append([NVCC] + FLAGS + ["-c", src, "-o", obj])
+
+    def run(cmd):
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        return cmd, r
+
+    logs = []
+    with ThreadPoolExecutor(max_workers=min(8, max(1, len(jobs)))) as ex:
+        for cmd, r in ex.map(run, jobs):
+            logs.append((cmd, r))
+            if r.returncode != 0:
+                raise RuntimeError("nvcc failed: " + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+            if verbose:
+                print(" ".join(cmd))
+                print(r.stderr)
+    if jobs or force or _stale(LIB, objs):
+        cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-ccbin", "g++"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("link failed: " + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+    with open(os.path.join(LIBDIR, "ptxas.log"), "a" if not force else "w") as f:
+        for cmd, r in logs:
+            f.write("### " + " ".join(cmd) + "\n" + r.stderr + "\n")
+    return LIB
+
+
+if __name__ == "__main__":
+    path = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
+    print(path)

@@ -1,0 +1,263 @@
+// lin_interp.cu -- fused bracket search + linear interpolation, reference layout.
+//
+// Replaces the per-column loops around ekat::LinInterp::setup and ::lin_interp
+// (reference: src/algorithm/ekat_lin_interp_impl.hpp:160-186 setup_impl with
+// src/kokkos/ekat_upper_bound.hpp:28-50, and :89-158 lin_interp_impl).
+//
+// Layout is the reference's: x1,y1 [ncol][pitch1], x2,y2 [ncol][pitch2], so a tile
+// of CB whole columns is ONE contiguous range per array. A persistent CTA streams
+// tiles through a 2-stage shared-memory ring with TMA bulk copies
+// (cp.async.bulk + mbarrier complete_tx): while the warps search/interpolate tile n
+// out of stage n&1, the copy engine fills the other stage with tile n+1. Source
+// coordinates, source fields and target coordinates are all staged; the index map
+// never leaves the SM unless the caller asks for it (m_indx_map parity).
+// Each lane owns one target level: a 32-wide group of consecutive targets of one
+// column per warp step, so x2 reads, the optional map and y2 writes are coalesced
+// and the bracket gathers hit neighbouring shared-memory words.
+//
+// Arithmetic is the reference's, unfused and in its order (:153-156):
+//     y2  = y1[k1ph] - y1[k1];  y2 *= x2 - x1[k1];  y2 /= x1[k1ph] - x1[k1];  y2 += y1[k1]
+// so results are bit-identical to the reference at -ffp-contract=off, for any Pack size
+// (pack padding is skipped: only the first km1 / km2 entries of a row are touched as data).
+#include "common.cuh"
+
+namespace ekb {
+
+// --------------------------------------------------------------- TMA / mbarrier helpers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// 1D bulk copy global -> shared, completion counted in bytes on `bar`. 16-byte aligned, size % 16 == 0.
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+
+enum LiMode { LI_FUSED = 0, LI_SETUP = 1, LI_APPLY = 2 };
+
+// upper_bound over x1[0..km1): first index with x1 > v (same predicate `v >= *it` as
+// ekat_upper_bound.hpp:37-48), select form instead of branches.
+template <typename R>
+__device__ __forceinline__ int bracket(const R* __restrict__ x1, int km1, R v) {
+  int lo = 0, n = km1;
+  while (n > 0) {
+    const int step = n >> 1, it = lo + step;
+    const bool ge = v >= x1[it];
+    lo = ge ? it + 1 : lo;
+    n = ge ? n - step - 1 : step;
+  }
+  return lo > 0 ? lo - 1 : lo;  // :179-181
+}
+
+struct LiArgs {
+  const void *x1, *x2, *y1;
+  void* y2;
+  int* indx;
+  const int* indx_in;
+  int64_t ncol, pitch1, pitch2, y1_fstride, y2_fstride;
+  int km1, km2, nfields, CB, use_tma;
+};
+
+template <typename R, int MODE>
+__global__ void __launch_bounds__(256) k_lin_interp(const LiArgs a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t bars[2];
+
+  const R* __restrict__ gx1 = static_cast<const R*>(a.x1);
+  const R* __restrict__ gx2 = static_cast<const R*>(a.x2);
+  const R* __restrict__ gy1 = static_cast<const R*>(a.y1);
+  R* __restrict__ gy2 = static_cast<R*>(a.y2);
+  const int km1 = a.km1, km2 = a.km2, CB = a.CB;
+  const int nf = MODE == LI_SETUP ? 0 : a.nfields;
+  const bool need_x2 = true;  // x2 drives the search (setup/fused) and enters the formula (apply/fused)
+  // stage layout: x1[CB*pitch1] | y1[nf][CB*pitch1] | x2[CB*pitch2], each 16B-aligned
+  const size_t n1 = (size_t)CB * a.pitch1, n2 = (size_t)CB * a.pitch2;
+  const size_t n1p = (n1 * sizeof(R) + 15) / 16 * 16 / sizeof(R), n2p = (n2 * sizeof(R) + 15) / 16 * 16 / sizeof(R);
+  const size_t stage_elems = n1p * (1 + nf) + n2p;
+  R* stage0 = reinterpret_cast<R*>(smem_raw);
+
+  const int64_t ntiles = (a.ncol + CB - 1) / CB;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  const int chunks = (km2 + 31) / 32;
+
+  if (tid == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  // issue the loads of tile `tile` into stage `s` (TMA when the tile is full and aligned)
+  auto issue = [&](int64_t tile, int s) {
+    const int64_t c0 = tile * CB;
+    const int nc = (int)tmin<int64_t>(CB, a.ncol - c0);
+    R* sx1 = stage0 + (size_t)s * stage_elems;
+    R* sy1 = sx1 + n1p;
+    R* sx2 = sy1 + n1p * nf;
+    const bool tma = a.use_tma && nc == CB;
+    if (tma) {
+      if (tid == 0) {
+        fence_proxy_async();
+        const unsigned b1 = (unsigned)(n1 * sizeof(R)), b2 = (unsigned)(n2 * sizeof(R));
+        mbar_expect_tx(&bars[s], b1 * (1 + nf) + (need_x2 ? b2 : 0));
+        tma_load_1d(sx1, gx1 + (size_t)c0 * a.pitch1, b1, &bars[s]);
+        for (int f = 0; f < nf; ++f)
+          tma_load_1d(sy1 + n1p * f, gy1 + (size_t)f * a.y1_fstride + (size_t)c0 * a.pitch1, b1, &bars[s]);
+        if (need_x2) tma_load_1d(sx2, gx2 + (size_t)c0 * a.pitch2, b2, &bars[s]);
+      }
+    } else {
+      // ragged or unaligned tile: plain coalesced loads (only real data, never the pack padding)
+      for (int c = warp; c < nc; c += nwarp) {
+        for (int k = lane; k < km1; k += 32) {
+          sx1[(size_t)c * a.pitch1 + k] = gx1[(size_t)(c0 + c) * a.pitch1 + k];
+          for (int f = 0; f < nf; ++f)
+            sy1[n1p * f + (size_t)c * a.pitch1 + k] = gy1[(size_t)f * a.y1_fstride + (size_t)(c0 + c) * a.pitch1 + k];
+        }
+        for (int k = lane; k < km2; k += 32) sx2[(size_t)c * a.pitch2 + k] = gx2[(size_t)(c0 + c) * a.pitch2 + k];
+      }
+    }
+    return tma;
+  };
+
+  unsigned phase_bits = 0;  // bit s = parity to wait for on stage s
+  int64_t tile = blockIdx.x;
+  bool cur_tma = false;
+  if (tile < ntiles) cur_tma = issue(tile, 0);
+  for (int it = 0; tile < ntiles; tile += gridDim.x, ++it) {
+    const int s = it & 1;
+    const int64_t next = tile + gridDim.x;
+    bool next_tma = false;
+    // stage s^1 was fully consumed before the __syncthreads that ended the previous iteration
+    if (next < ntiles) next_tma = issue(next, s ^ 1);
+    if (cur_tma) {
+      mbar_wait(&bars[s], (phase_bits >> s) & 1u);
+      phase_bits ^= 1u << s;
+    } else {
+      __syncthreads();  // plain loads of this stage were written by other warps (previous iteration / prologue)
+    }
+
+    const int64_t c0 = tile * CB;
+    const int nc = (int)tmin<int64_t>(CB, a.ncol - c0);
+    const R* sx1 = stage0 + (size_t)s * stage_elems;
+    const R* sy1 = sx1 + n1p;
+    const R* sx2 = sy1 + n1p * nf;
+    for (int u = warp; u < nc * chunks; u += nwarp) {
+      const int c = u / chunks, k2 = (u - c * chunks) * 32 + lane;
+      if (k2 < km2) {
+        const R* x1c = sx1 + (size_t)c * a.pitch1;
+        const R xt = sx2[(size_t)c * a.pitch2 + k2];
+        int k1;
+        if (MODE == LI_APPLY) k1 = a.indx_in[(size_t)(c0 + c) * km2 + k2];
+        else k1 = bracket<R>(x1c, km1, xt);
+        if (MODE != LI_APPLY && a.indx) a.indx[(size_t)(c0 + c) * km2 + k2] = k1;
+        if (MODE != LI_SETUP) {
+          const int k1ph = k1 == km1 - 1 ? k1 - 1 : k1 + 1;  // :119-131
+          const R xa = x1c[k1], xb = x1c[k1ph];
+          const R dxt = x_sub(xt, xa), dx = x_sub(xb, xa);
+          for (int f = 0; f < nf; ++f) {
+            const R* y1c = sy1 + n1p * f + (size_t)c * a.pitch1;
+            const R ya = y1c[k1], yb = y1c[k1ph];
+            R v = x_sub(yb, ya);  // :153
+            v = x_mul(v, dxt);    // :154
+            v = x_div(v, dx);     // :155
+            v = x_add(v, ya);     // :156
+            st_stream(gy2 + (size_t)f * a.y2_fstride + (size_t)(c0 + c) * a.pitch2 + k2, v);
+          }
+        }
+      }
+    }
+    __syncthreads();  // everyone is done with stage s before it is refilled two iterations from now
+    cur_tma = next_tma;
+  }
+}
+
+template <typename R>
+int lin_interp(int mode, const R* x1, const R* x2, const R* y1, R* y2, int* indx, const int* indx_in,
+               int64_t ncol, int km1, int km2, int64_t pitch1, int64_t pitch2, int nfields, int64_t y1_fstride,
+               int64_t y2_fstride, cudaStream_t stream) {
+  if (ncol == 0 || km2 == 0) return EKAT_B200_OK;
+  if (mode != LI_SETUP && nfields == 0) {
+    if (mode == LI_APPLY || !indx) return EKAT_B200_OK;
+    mode = LI_SETUP;
+  }
+  const int nf = mode == LI_SETUP ? 0 : nfields;
+  const size_t col_bytes = ((size_t)pitch1 * (1 + nf) + pitch2) * sizeof(R);
+  // columns per tile: ~24 KB stages so that 3+ CTAs (2 stages each) share an SM
+  const Tuning tu = tuning();
+  int CB = tu.cols_per_cta > 0 ? tu.cols_per_cta : (int)((24 * 1024) / col_bytes);
+  if (CB > 64) CB = 64;
+  if (CB > 1) CB &= ~1;  // even -> tile byte counts are multiples of 16 for f64
+  if (sizeof(R) == 4 && CB > 3) CB &= ~3;
+  if (CB < 1) CB = 1;
+  size_t smem;
+  for (;;) {
+    const size_t n1p = ((size_t)CB * pitch1 * sizeof(R) + 15) / 16 * 16, n2p = ((size_t)CB * pitch2 * sizeof(R) + 15) / 16 * 16;
+    smem = 2 * (n1p * (1 + nf) + n2p);
+    if (smem <= kMaxSmemPerCta || CB == 1) break;
+    CB /= 2;
+  }
+  if (smem > kMaxSmemPerCta) return EKAT_B200_ERR_TOO_LARGE;
+  auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  const bool sizes_ok = ((size_t)CB * pitch1 * sizeof(R)) % 16 == 0 && ((size_t)CB * pitch2 * sizeof(R)) % 16 == 0 &&
+                        ((size_t)y1_fstride * sizeof(R)) % 16 == 0;
+  const bool use_tma = tu.variant != 1 && sizes_ok && aligned16(x1) && aligned16(x2) && (nf == 0 || aligned16(y1));
+
+  LiArgs a;
+  a.x1 = x1; a.x2 = x2; a.y1 = y1; a.y2 = y2; a.indx = indx; a.indx_in = indx_in;
+  a.ncol = ncol; a.pitch1 = pitch1; a.pitch2 = pitch2; a.y1_fstride = y1_fstride; a.y2_fstride = y2_fstride;
+  a.km1 = km1; a.km2 = km2; a.nfields = nfields; a.CB = CB; a.use_tma = use_tma ? 1 : 0;
+
+  const int64_t ntiles = (ncol + CB - 1) / CB;
+  int per_sm = (int)(kMaxSmemPerCta / (smem + 1024));
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 8) per_sm = 8;
+  const unsigned grid = (unsigned)tmin<int64_t>(ntiles, (int64_t)kNumSms * per_sm);
+  int rc;
+  const char* name;
+  if (mode == LI_FUSED) {
+    auto k = k_lin_interp<R, LI_FUSED>;
+    if ((rc = allow_smem(k, smem))) return rc;
+    k<<<grid, 256, smem, stream>>>(a);
+    name = sizeof(R) == 8 ? "lin_interp<f64,fused>" : "lin_interp<f32,fused>";
+  } else if (mode == LI_SETUP) {
+    auto k = k_lin_interp<R, LI_SETUP>;
+    if ((rc = allow_smem(k, smem))) return rc;
+    k<<<grid, 256, smem, stream>>>(a);
+    name = sizeof(R) == 8 ? "lin_interp<f64,setup>" : "lin_interp<f32,setup>";
+  } else {
+    auto k = k_lin_interp<R, LI_APPLY>;
+    if ((rc = allow_smem(k, smem))) return rc;
+    k<<<grid, 256, smem, stream>>>(a);
+    name = sizeof(R) == 8 ? "lin_interp<f64,apply>" : "lin_interp<f32,apply>";
+  }
+  note_launch(name);
+  return check_cuda(cudaGetLastError());
+}
+
+template int lin_interp<double>(int, const double*, const double*, const double*, double*, int*, const int*, int64_t,
+                                int, int, int64_t, int64_t, int, int64_t, int64_t, cudaStream_t);
+template int lin_interp<float>(int, const float*, const float*, const float*, float*, int*, const int*, int64_t, int,
+                               int, int64_t, int64_t, int, int64_t, int64_t, cudaStream_t);
+
+}  // namespace ekb

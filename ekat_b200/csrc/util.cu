@@ -1,0 +1,264 @@
+// util.cu -- synthetic-input fills, layout marshalling and verification reductions.
+//
+//  * fills: bit-identical to the reference's deterministic test fills
+//    (tests/algorithm/tridiag_tests.hpp:11-28 fill_tridiag_matrix, :30-40 fill_data_matrix,
+//    driven per problem as tests/algorithm/tridiag_tests_performance.cpp:190-196) and to the
+//    counter-based LinInterp coordinates of SURVEY.md section 8d (ekat_b200/synth.py is the
+//    numpy statement of the same generator).
+//  * transposes: [ncol][n] <-> [n][pitch].
+//  * checksum / residual: device-scalar reductions feeding one NCCL all-reduce (section 8e);
+//    residual = the reference's acceptance norm (tests/algorithm/tridiag_tests.hpp:42-106).
+#include "common.cuh"
+
+namespace ekb {
+
+// ----------------------------------------------------------------------------- fills
+template <typename R>
+__global__ void k_fill_tridiag(R* __restrict__ dl, R* __restrict__ d, R* __restrict__ du, R* __restrict__ X,
+                               int64_t ncol, int64_t col0, int nlev, int nA, int nrhs, int64_t a_stride,
+                               int64_t x_stride, int lev_major, int seed_mod) {
+  // one thread per (level, column); loops over the nA matrices / nrhs right-hand sides
+  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = blockIdx.y;
+  if (c >= ncol) return;
+  const int seed = (int)(seed_mod > 0 ? (col0 + c) % seed_mod : (col0 + c));
+  for (int p = 0; p < nA; ++p) {
+    const int k = seed + p + i;
+    // dl = (k%5==0 ? -1 : 1) * 1.3 * (0.1 + ((k*k) % 11)), evaluated in double, left to right
+    const double vdl = x_mul(x_mul(k % 5 == 0 ? -1.0 : 1.0, 1.3), x_add(0.1, (double)((k * k) % 11)));
+    const double vdu = x_mul(x_mul(k % 7 == 0 ? -1.0 : 1.0, 1.7), x_add(0.2, (double)((k * k) % 13)));
+    const R rdl = (R)vdl, rdu = (R)vdu;
+    // d = (k%3==0 ? -1 : 1) * (0.7 + |dl| + |du| + (k % 17)) with dl, du already rounded to R
+    const double s = x_add(x_add(x_add(0.7, fabs((double)rdl)), fabs((double)rdu)), (double)(k % 17));
+    const R rd = (R)x_mul(k % 3 == 0 ? -1.0 : 1.0, s);
+    const size_t o = lev_major ? ((size_t)p * nlev + i) * a_stride + c : (size_t)c * a_stride + (size_t)i * nA + p;
+    dl[o] = rdl;
+    du[o] = rdu;
+    d[o] = rd;
+  }
+  if (X) {
+    const int seedx = nrhs;  // fill_data_matrix(X, in.nrhs)
+    for (int j = 0; j < nrhs; ++j) {
+      const int sg = (7 * i + 11 * j + 3 * i * j) % 3 == 0 ? -1 : 1;
+      const int m = (17 * (i - 19) + 13 * (j - 11) + 5 * (i - 5) * (j - 7) + seedx) % 47;
+      const size_t o = lev_major ? ((size_t)j * nlev + i) * x_stride + c : (size_t)c * x_stride + (size_t)i * nrhs + j;
+      X[o] = (R)x_mul(x_mul((double)sg, 1.7), (double)m);
+    }
+  }
+}
+
+__host__ __device__ __forceinline__ uint64_t splitmix64(uint64_t z) {
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+__device__ __forceinline__ double unit_rand(uint64_t key, unsigned stream, unsigned k) {
+  const uint64_t v = splitmix64(key + ((uint64_t)stream << 32) + k);
+  return (double)(v >> 11) * (1.0 / 9007199254740992.0);  // [0,1), 53 bits
+}
+
+// One thread per column (the cumulative sums are sequential by construction).
+//   x1[0] = u, x1[k] = x1[k-1] + (0.1 + 0.9 u)      strictly increasing (lin_interp_test.cpp:182-216)
+//   y1[k] = 100 u
+//   x2[k] = lo + (hi - lo) * (c_k / W), c_k = sum_{m<=k} (0.05 + u_m), W = c_{km2-1} + (0.05 + u_extra)
+//           lo/hi = x1[0] + delta/1000, x1[km1-1] - delta/1000     (lin_interp_test.cpp:386-390)
+template <typename R>
+__global__ void k_fill_lin_interp(R* __restrict__ x1, R* __restrict__ y1, R* __restrict__ x2, int64_t ncol,
+                                  int64_t col0, int km1, int km2, int64_t pitch1, int64_t pitch2, int lev_major,
+                                  uint64_t seed) {
+  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ncol) return;
+  const uint64_t key = splitmix64(seed ^ splitmix64((uint64_t)(col0 + c)));
+  double acc = 0, first = 0;
+  for (int k = 0; k < km1; ++k) {
+    const double u = unit_rand(key, 0, k);
+    acc = k == 0 ? u : x_add(acc, x_add(0.1, x_mul(0.9, u)));
+    if (k == 0) first = acc;
+    const size_t o = lev_major ? (size_t)k * pitch1 + c : (size_t)c * pitch1 + k;
+    x1[o] = (R)acc;
+    if (y1) y1[o] = (R)x_mul(100.0, unit_rand(key, 1, k));
+  }
+  if (!x2 || km2 <= 0) return;
+  const double last = acc, delta = x_sub(last, first);
+  const double lo = x_add(first, x_div(delta, 1000.0)), hi = x_sub(last, x_div(delta, 1000.0));
+  double W = 0;
+  for (int k = 0; k <= km2; ++k) W = x_add(W, x_add(0.05, unit_rand(key, 2, k)));
+  double ck = 0;
+  for (int k = 0; k < km2; ++k) {
+    ck = x_add(ck, x_add(0.05, unit_rand(key, 2, k)));
+    const size_t o = lev_major ? (size_t)k * pitch2 + c : (size_t)c * pitch2 + k;
+    x2[o] = (R)x_add(lo, x_mul(x_sub(hi, lo), x_div(ck, W)));
+  }
+}
+
+// ------------------------------------------------------------------------ transposes
+// src[c*src_stride + k] -> dst[k*pitch + c], 32x32 tiles through padded shared memory.
+template <typename R>
+__global__ void k_col_to_lev(const R* __restrict__ src, R* __restrict__ dst, int64_t ncol, int n,
+                             int64_t src_stride, int64_t pitch) {
+  __shared__ R tile[32][33];
+  const int64_t c0 = (int64_t)blockIdx.x * 32;
+  const int k0 = blockIdx.y * 32;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int64_t c = c0 + r;
+    const int k = k0 + threadIdx.x;
+    if (c < ncol && k < n) tile[r][threadIdx.x] = src[(size_t)c * src_stride + k];
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int k = k0 + r;
+    const int64_t c = c0 + threadIdx.x;
+    if (c < ncol && k < n) dst[(size_t)k * pitch + c] = tile[threadIdx.x][r];
+  }
+}
+template <typename R>
+__global__ void k_lev_to_col(const R* __restrict__ src, R* __restrict__ dst, int64_t ncol, int n, int64_t pitch,
+                             int64_t dst_stride) {
+  __shared__ R tile[32][33];
+  const int64_t c0 = (int64_t)blockIdx.x * 32;
+  const int k0 = blockIdx.y * 32;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int k = k0 + r;
+    const int64_t c = c0 + threadIdx.x;
+    if (c < ncol && k < n) tile[r][threadIdx.x] = src[(size_t)k * pitch + c];
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int64_t c = c0 + r;
+    const int k = k0 + threadIdx.x;
+    if (c < ncol && k < n) dst[(size_t)c * dst_stride + k] = tile[threadIdx.x][r];
+  }
+}
+
+// ------------------------------------------------------------------------ reductions
+template <typename R> struct Bits;
+template <> struct Bits<double> { static __device__ uint64_t of(double v) { return (uint64_t)__double_as_longlong(v); } };
+template <> struct Bits<float> { static __device__ uint64_t of(float v) { return (uint64_t)__float_as_uint(v); } };
+
+template <typename R>
+__global__ void k_checksum(const R* __restrict__ a, int64_t nrows, int64_t ncol, int64_t pitch,
+                           unsigned long long* out) {
+  uint64_t s = 0;
+  const int64_t total = nrows * ncol;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = idx / ncol, c = idx - r * ncol;
+    s += Bits<R>::of(a[(size_t)r * pitch + c]);
+  }
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  __shared__ uint64_t ws[32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) ws[w] = s;
+  __syncthreads();
+  if (w == 0) {
+    s = lane < (blockDim.x + 31) / 32 ? ws[lane] : 0;
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) atomicAdd(out, (unsigned long long)s);
+  }
+}
+
+// thread per column; y = A x evaluated in R with unfused ops in the reference's order
+// (tridiag_tests.hpp:62-85), |b - y| and |b| maxima in double (:96-105).
+template <typename R>
+__global__ void k_residual(const R* __restrict__ dl, const R* __restrict__ d, const R* __restrict__ du,
+                           const R* __restrict__ B, const R* __restrict__ X, int64_t ncol, int nlev, int nA,
+                           int nrhs, int64_t pitch, unsigned long long* out) {
+  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  double worst = 0;
+  if (c < ncol) {
+    double num = 0, den = 0;
+    for (int j = 0; j < nrhs; ++j) {
+      const size_t am = (size_t)(nA > 1 ? j : 0) * nlev, xm = (size_t)j * nlev;
+      R xm1 = 0, x0 = X[xm * pitch + c];
+      for (int i = 0; i < nlev; ++i) {
+        const R xp1 = i + 1 < nlev ? X[(xm + i + 1) * pitch + c] : (R)0;
+        const size_t a = (am + i) * pitch + c;
+        R y;
+        if (nlev == 1) y = x_mul(d[a], x0);
+        else if (i == 0) y = x_add(x_mul(d[a], x0), x_mul(du[a], xp1));
+        else if (i == nlev - 1) y = x_add(x_mul(dl[a], xm1), x_mul(d[a], x0));
+        else y = x_add(x_add(x_mul(dl[a], xm1), x_mul(d[a], x0)), x_mul(du[a], xp1));
+        const double bb = (double)B[(xm + i) * pitch + c];
+        if (!isfinite((double)y)) { num = __longlong_as_double(0x7ff0000000000000LL); den = 1; }
+        num = fmax(num, fabs(bb - (double)y));
+        den = fmax(den, fabs(bb));
+        xm1 = x0;
+        x0 = xp1;
+      }
+    }
+    worst = den > 0 ? num / den : num;
+  }
+  for (int o = 16; o > 0; o >>= 1) worst = fmax(worst, __shfl_xor_sync(0xffffffffu, worst, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(out, (unsigned long long)__double_as_longlong(worst));  // >= 0: bit order == value order
+}
+
+// ------------------------------------------------------------------------ host side
+template <typename R>
+int fill_tridiag(R* dl, R* d, R* du, R* X, int64_t ncol, int64_t col0, int nlev, int nA, int nrhs,
+                 int64_t a_stride, int64_t x_stride, int layout, int seed_mod, cudaStream_t st) {
+  if (ncol == 0) return EKAT_B200_OK;
+  dim3 grid((unsigned)((ncol + 127) / 128), (unsigned)nlev);
+  k_fill_tridiag<R><<<grid, 128, 0, st>>>(dl, d, du, X, ncol, col0, nlev, nA, nrhs, a_stride, x_stride,
+                                          layout == EKAT_B200_LAYOUT_LEV_MAJOR, seed_mod);
+  note_launch("fill_tridiag");
+  return check_cuda(cudaGetLastError());
+}
+template <typename R>
+int fill_lin_interp(R* x1, R* y1, R* x2, int64_t ncol, int64_t col0, int km1, int km2, int64_t pitch1,
+                    int64_t pitch2, int layout, uint64_t seed, cudaStream_t st) {
+  if (ncol == 0) return EKAT_B200_OK;
+  k_fill_lin_interp<R><<<(unsigned)((ncol + 127) / 128), 128, 0, st>>>(
+      x1, y1, x2, ncol, col0, km1, km2, pitch1, pitch2, layout == EKAT_B200_LAYOUT_LEV_MAJOR, seed);
+  note_launch("fill_lin_interp");
+  return check_cuda(cudaGetLastError());
+}
+template <typename R>
+int col_to_lev(const R* src, R* dst, int64_t ncol, int n, int64_t src_stride, int64_t pitch, cudaStream_t st) {
+  if (ncol == 0 || n == 0) return EKAT_B200_OK;
+  dim3 grid((unsigned)((ncol + 31) / 32), (unsigned)((n + 31) / 32)), block(32, 8);
+  k_col_to_lev<R><<<grid, block, 0, st>>>(src, dst, ncol, n, src_stride, pitch);
+  note_launch("col_to_lev");
+  return check_cuda(cudaGetLastError());
+}
+template <typename R>
+int lev_to_col(const R* src, R* dst, int64_t ncol, int n, int64_t pitch, int64_t dst_stride, cudaStream_t st) {
+  if (ncol == 0 || n == 0) return EKAT_B200_OK;
+  dim3 grid((unsigned)((ncol + 31) / 32), (unsigned)((n + 31) / 32)), block(32, 8);
+  k_lev_to_col<R><<<grid, block, 0, st>>>(src, dst, ncol, n, pitch, dst_stride);
+  note_launch("lev_to_col");
+  return check_cuda(cudaGetLastError());
+}
+template <typename R>
+int checksum(const R* a, int64_t nrows, int64_t ncol, int64_t pitch, uint64_t* out, cudaStream_t st) {
+  if (nrows * ncol == 0) return EKAT_B200_OK;
+  const int64_t total = nrows * ncol;
+  const unsigned blocks = (unsigned)tmin<int64_t>((total + 255) / 256, (int64_t)kNumSms * 16);
+  k_checksum<R><<<blocks, 256, 0, st>>>(a, nrows, ncol, pitch, reinterpret_cast<unsigned long long*>(out));
+  note_launch("checksum");
+  return check_cuda(cudaGetLastError());
+}
+template <typename R>
+int residual(const R* dl, const R* d, const R* du, const R* B, const R* X, int64_t ncol, int nlev, int nA,
+             int nrhs, int64_t pitch, double* out, cudaStream_t st) {
+  if (ncol == 0) return EKAT_B200_OK;
+  k_residual<R><<<(unsigned)((ncol + 127) / 128), 128, 0, st>>>(dl, d, du, B, X, ncol, nlev, nA, nrhs, pitch,
+                                                             reinterpret_cast<unsigned long long*>(out));
+  note_launch("residual");
+  return check_cuda(cudaGetLastError());
+}
+
+#define INST(R)                                                                                              \
+  template int fill_tridiag<R>(R*, R*, R*, R*, int64_t, int64_t, int, int, int, int64_t, int64_t, int, int,   \
+                               cudaStream_t);                                                                \
+  template int fill_lin_interp<R>(R*, R*, R*, int64_t, int64_t, int, int, int64_t, int64_t, int, uint64_t,   \
+                                  cudaStream_t);                                                             \
+  template int col_to_lev<R>(const R*, R*, int64_t, int, int64_t, int64_t, cudaStream_t);                    \
+  template int lev_to_col<R>(const R*, R*, int64_t, int, int64_t, int64_t, cudaStream_t);                    \
+  template int checksum<R>(const R*, int64_t, int64_t, int64_t, uint64_t*, cudaStream_t);                    \
+  template int residual<R>(const R*, const R*, const R*, const R*, const R*, int64_t, int, int, int, int64_t, \
+                           double*, cudaStream_t);
+INST(double)
+INST(float)
+
+}  // namespace ekb

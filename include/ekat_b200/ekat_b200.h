@@ -1,0 +1,260 @@
+/* ekat_b200.h -- C ABI of libekat_b200.so: B200 (sm_100a) kernels for EKAT's
+ * Algorithm-package hot path (batched tridiagonal solvers + LinInterp).
+ *
+ * The reference has no FFI: the path is a set of header-only *team-level device
+ * functions* that a caller invokes once per column from inside its own Kokkos
+ * team kernel. A hand-written CUDA kernel cannot be
+ * inlined into someone else's kernel, so the drop-in unit is the whole batch
+ * idiom
+ *     parallel_for(TeamPolicy(ncol, ...), [=](team){ slice column; solver(team, ...); })
+ * (tests/algorithm/tridiag_tests_performance.cpp:204-226,
+ *  tests/algorithm/lin_interp_test.cpp:141-154), and each entry point below
+ * replaces one such loop. The C++ adapters in ekat_tridiag.hpp /
+ * ekat_lin_interp.hpp keep the reference's names on top of this ABI.
+ *
+ * Conventions
+ *  - every data pointer is a DEVICE pointer unless the name says "host";
+ *  - asynchronous on `stream` (a cudaStream_t; 0 = legacy default stream);
+ *  - no global state, no allocation, no synchronisation inside;
+ *  - returns EKAT_B200_OK or a negative ekat_b200_status; never throws, never
+ *    aborts (the reference's debug `assert`s and EKAT_KERNEL_REQUIRE aborts,
+ *    src/algorithm/ekat_tridiag.hpp:184-185,328-330 and
+ *    src/pack/ekat_pack_kokkos.hpp:266-267, become EKAT_B200_ERR_INVALID);
+ *  - zero-size batches (ncol == 0, or km2 == 0 for LinInterp) are a no-op
+ *    (tests/algorithm/lin_interp_test.cpp:47-92);
+ *  - diagonal dominance / sorted x1 are the caller's contract, as in the
+ *    reference (src/algorithm/ekat_tridiag.hpp:12-17); nothing is checked.
+ *
+ * There is no CPU fallback anywhere in this library.
+ */
+#ifndef EKAT_B200_H
+#define EKAT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EKAT_B200_VERSION 100 /* 0.1.0 */
+
+typedef struct CUstream_st* ekat_b200_stream_t; /* == cudaStream_t */
+
+typedef enum {
+  EKAT_B200_OK = 0,
+  EKAT_B200_ERR_INVALID = -1,     /* bad shape / null pointer / misaligned pitch */
+  EKAT_B200_ERR_UNSUPPORTED = -2, /* valid in the reference, not built here */
+  EKAT_B200_ERR_CUDA = -3,        /* a CUDA runtime call failed; see ekat_b200_last_cuda_error */
+  EKAT_B200_ERR_TOO_LARGE = -4    /* one column does not fit the kernel's on-chip staging */
+} ekat_b200_status;
+
+/* ------------------------------------------------------------------------
+ * Data layouts for the batched tridiagonal solvers.
+ *
+ * EKAT_B200_LAYOUT_COL_MAJOR -- the reference's: every column's levels are
+ *   contiguous (LayoutRight views sliced per column,
+ *   tests/algorithm/tridiag_tests_performance.cpp:90-124,181-185).
+ *     dl/d/du element (col c, level i, matrix p) at  base[c*a_stride + i*nA   + p]
+ *     X       element (col c, level i, rhs j)    at  X   [c*x_stride + i*nrhs + j]
+ *   a_stride >= nlev*nA, x_stride >= nlev*nrhs (elements). For the perf-test
+ *   array A[ncol][3][nlev][nA]: dl=A, d=A+nlev*nA, du=A+2*nlev*nA, a_stride=3*nlev*nA.
+ *
+ * EKAT_B200_LAYOUT_LEV_MAJOR -- native: columns are the fastest index, so one
+ *   level step of a warp is one coalesced access.
+ *     dl/d/du element (c, i, p) at  base[(p*nlev + i)*a_stride + c]
+ *     X       element (c, i, j) at  X   [(j*nlev + i)*x_stride + c]
+ *   a_stride, x_stride >= ncol = column pitch in elements.
+ * ---------------------------------------------------------------------- */
+typedef enum { EKAT_B200_LAYOUT_COL_MAJOR = 0, EKAT_B200_LAYOUT_LEV_MAJOR = 1 } ekat_b200_layout;
+
+/* flags */
+#define EKAT_B200_CLOBBER_DIAGS 1u /* also write the factorisation back into dl/d, as the reference's
+                                      in-place solvers do (ekat_tridiag.hpp:44-47). Default: dl,d,du are
+                                      read-only, which saves 2 of 7 words of HBM traffic per level. */
+
+/* ------------------------------------------------------------------------
+ * Batched tridiagonal solvers: X <- A^-1 X for ncol independent columns.
+ *   nA   = 1 (one matrix per column, shared by its nrhs right-hand sides) or
+ *          nrhs (one matrix per right-hand side)       -- problem formats 1-3,
+ *          src/algorithm/ekat_tridiag.hpp:18-31; bfb's "nA==1 && nrhs>1" rule :658-661.
+ *   dl(0) and du(nlev-1) are never used (:24-27) but must be readable.
+ *
+ * thomas : replaces the loop around ekat::tridiag::thomas (team :323-334 and
+ *          serial :336-381). Fused-multiply-add and reciprocal form allowed;
+ *          agrees with the reference to 1e-13 (f64) / 1e-5 (f32) relative.
+ * bfb    : replaces the loop around ekat::tridiag::bfb (:632-678). Fixed
+ *          operation order, separately rounded * and -, IEEE division:
+ *          bit-identical to the reference built with -ffp-contract=off.
+ * cr     : replaces the loop around ekat::tridiag::cr (:385-630). Same update
+ *          formulas and order as the reference, unfused: bit-identical to the
+ *          reference's cyclic reduction built with -ffp-contract=off.
+ * ---------------------------------------------------------------------- */
+#define EKAT_B200_DECL_TRIDIAG(name, T)                                                              \
+  int name(T* dl, T* d, T* du, T* X, int64_t ncol, int nlev, int nA, int nrhs, int64_t a_stride,     \
+           int64_t x_stride, int layout, unsigned flags, ekat_b200_stream_t stream)
+EKAT_B200_DECL_TRIDIAG(ekat_b200_tridiag_thomas_f64, double);
+EKAT_B200_DECL_TRIDIAG(ekat_b200_tridiag_thomas_f32, float);
+EKAT_B200_DECL_TRIDIAG(ekat_b200_tridiag_bfb_f64, double);
+EKAT_B200_DECL_TRIDIAG(ekat_b200_tridiag_bfb_f32, float);
+EKAT_B200_DECL_TRIDIAG(ekat_b200_tridiag_cr_f64, double);
+EKAT_B200_DECL_TRIDIAG(ekat_b200_tridiag_cr_f32, float);
+
+/* ------------------------------------------------------------------------
+ * LinInterp: 1D vertical linear interpolation of y1(x1) onto x2, per column.
+ * Layout is the reference's (src/algorithm/ekat_lin_interp_impl.hpp:12-19,
+ * scalarized Pack views, src/pack/ekat_pack_kokkos.hpp:166-279):
+ *     x1, y1 : [ncol][pitch1]   only the first km1 entries of a row are data
+ *     x2, y2 : [ncol][pitch2]   only the first km2 entries of a row are data
+ *   pitch = npack(km)*N elements for a Pack<T,N> view (N = 1: pitch = km).
+ *   Padding lanes are neither read as data nor written.
+ *   nfields fields sharing (x1, x2): field f of y1 at y1 + f*y1_fstride, of y2
+ *   at y2 + f*y2_fstride (elements).
+ *   indx_map: [ncol][km2] ints, the bracketing source index of every target
+ *   (LinInterp::m_indx_map, ekat_lin_interp.hpp:156).
+ *
+ * setup  : replaces the loop around LinInterp::setup  (impl :21-46,160-186).
+ * apply  : replaces the loop around LinInterp::lin_interp (impl :48-158) with
+ *          a map produced by setup.
+ * fused  : setup + lin_interp in one pass; the map stays on chip unless
+ *          indx_map != NULL.
+ * Results are bit-identical to the reference built with -ffp-contract=off
+ * (the 4-statement formula :153-156 in that order, IEEE division).
+ * km1 >= 2 is required when km2 > 0 (the reference reads x1[k1 +- 1]).
+ * ---------------------------------------------------------------------- */
+#define EKAT_B200_DECL_LI(T, sfx)                                                                        \
+  int ekat_b200_lin_interp_setup_##sfx(const T* x1, const T* x2, int* indx_map, int64_t ncol, int km1,   \
+                                       int km2, int64_t pitch1, int64_t pitch2, ekat_b200_stream_t s);   \
+  int ekat_b200_lin_interp_apply_##sfx(const T* x1, const T* x2, const T* y1, T* y2, const int* indx_map,\
+                                       int64_t ncol, int km1, int km2, int64_t pitch1, int64_t pitch2,   \
+                                       int nfields, int64_t y1_fstride, int64_t y2_fstride,              \
+                                       ekat_b200_stream_t s);                                            \
+  int ekat_b200_lin_interp_##sfx(const T* x1, const T* x2, const T* y1, T* y2, int* indx_map,            \
+                                 int64_t ncol, int km1, int km2, int64_t pitch1, int64_t pitch2,         \
+                                 int nfields, int64_t y1_fstride, int64_t y2_fstride, ekat_b200_stream_t s)
+EKAT_B200_DECL_LI(double, f64);
+EKAT_B200_DECL_LI(float, f32);
+
+/* ------------------------------------------------------------------------
+ * Fused "diffuse then remap" (BASELINE config 4): for every column solve the
+ * shared-A, nrhs-RHS system (thomas arithmetic) and interpolate each solution
+ * from source coordinates x1[nlev] onto x2[km2] without the solutions leaving
+ * the SM. All arrays LEV_MAJOR with one column pitch `pitch`:
+ *   dl,d,du: [nlev][pitch]  B: [nrhs][nlev][pitch]  x1: [nlev][pitch]
+ *   x2: [km2][pitch]        Y2: [nrhs][km2][pitch]
+ * X (nullable): [nrhs][nlev][pitch] also receives the un-remapped solutions.
+ * ---------------------------------------------------------------------- */
+int ekat_b200_tridiag_lin_interp_f64(const double* dl, const double* d, const double* du, const double* B,
+                                     const double* x1, const double* x2, double* Y2, double* X, int64_t ncol,
+                                     int nlev, int km2, int nrhs, int64_t pitch, ekat_b200_stream_t stream);
+int ekat_b200_tridiag_lin_interp_f32(const float* dl, const float* d, const float* du, const float* B,
+                                     const float* x1, const float* x2, float* Y2, float* X, int64_t ncol,
+                                     int nlev, int km2, int nrhs, int64_t pitch, ekat_b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Layout marshalling: [ncol][n] <-> [n][pitch] device
+ * transposes at copy speed, so callers holding reference-layout views can use
+ * the LEV_MAJOR kernels. src element (c,k) at src[c*src_stride + k].
+ * ---------------------------------------------------------------------- */
+int ekat_b200_col_to_lev_f64(const double* src, double* dst, int64_t ncol, int n, int64_t src_stride,
+                             int64_t pitch, ekat_b200_stream_t stream);
+int ekat_b200_col_to_lev_f32(const float* src, float* dst, int64_t ncol, int n, int64_t src_stride,
+                             int64_t pitch, ekat_b200_stream_t stream);
+int ekat_b200_lev_to_col_f64(const double* src, double* dst, int64_t ncol, int n, int64_t pitch,
+                             int64_t dst_stride, ekat_b200_stream_t stream);
+int ekat_b200_lev_to_col_f32(const float* src, float* dst, int64_t ncol, int n, int64_t pitch,
+                             int64_t dst_stride, ekat_b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Verification reductions for the column-sharded multi-GPU driver (SURVEY.md
+ * section 8e). Results are DEVICE scalars so they can go straight into one
+ * NCCL all-reduce (ekat::Comm::all_reduce, src/core/ekat_comm.hpp:152-162).
+ *  checksum : *out += wrap-around sum of the raw bit patterns (f32 zero-
+ *             extended) of the [nrows][ncol] block of a pitched array --
+ *             associative, hence identical for any column partition.
+ *  residual : *out = max(*out, max_c max|B - A X| / max|B|), the reference's
+ *             acceptance norm (tests/algorithm/tridiag_tests.hpp:42-106),
+ *             LEV_MAJOR operands, shared A (nA = 1) or nA = nrhs.
+ * ---------------------------------------------------------------------- */
+int ekat_b200_checksum_f64(const double* a, int64_t nrows, int64_t ncol, int64_t pitch, uint64_t* out,
+                           ekat_b200_stream_t stream);
+int ekat_b200_checksum_f32(const float* a, int64_t nrows, int64_t ncol, int64_t pitch, uint64_t* out,
+                           ekat_b200_stream_t stream);
+int ekat_b200_tridiag_residual_f64(const double* dl, const double* d, const double* du, const double* B,
+                                   const double* X, int64_t ncol, int nlev, int nA, int nrhs, int64_t pitch,
+                                   double* out, ekat_b200_stream_t stream);
+int ekat_b200_tridiag_residual_f32(const float* dl, const float* d, const float* du, const float* B,
+                                   const float* X, int64_t ncol, int nlev, int nA, int nrhs, int64_t pitch,
+                                   double* out, ekat_b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Synthetic inputs, generated on the device, bit-identical to the reference's
+ * deterministic fills (tests/algorithm/tridiag_tests.hpp:11-40 as driven at
+ * tests/algorithm/tridiag_tests_performance.cpp:190-196) with
+ * seed = (col0 + c) mod seed_mod, and to SURVEY.md section 8d's counter-based
+ * LinInterp coordinates. X may be NULL. Used by bench.py and the tests only.
+ * ---------------------------------------------------------------------- */
+int ekat_b200_fill_tridiag_f64(double* dl, double* d, double* du, double* X, int64_t ncol, int64_t col0,
+                               int nlev, int nA, int nrhs, int64_t a_stride, int64_t x_stride, int layout,
+                               int seed_mod, ekat_b200_stream_t stream);
+int ekat_b200_fill_tridiag_f32(float* dl, float* d, float* du, float* X, int64_t ncol, int64_t col0, int nlev,
+                               int nA, int nrhs, int64_t a_stride, int64_t x_stride, int layout, int seed_mod,
+                               ekat_b200_stream_t stream);
+int ekat_b200_fill_lin_interp_f64(double* x1, double* y1, double* x2, int64_t ncol, int64_t col0, int km1,
+                                  int km2, int64_t pitch1, int64_t pitch2, int layout, uint64_t seed,
+                                  ekat_b200_stream_t stream);
+int ekat_b200_fill_lin_interp_f32(float* x1, float* y1, float* x2, int64_t ncol, int64_t col0, int km1,
+                                  int km2, int64_t pitch1, int64_t pitch2, int layout, uint64_t seed,
+                                  ekat_b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Host-memory entry points: identical argument meaning, but every data pointer
+ * is a HOST pointer (pinned memory recommended) -- for callers that today run
+ * the reference on host views (tests/algorithm/tridiag_tests_performance.cpp:
+ * 260-303). Columns are cut into chunks that flow through a multi-stream
+ * upload -> solve -> download pipeline; device staging belongs to an explicit
+ * pipeline object (device_bytes split over nslots <= 8 slots, one stream each).
+ * Synchronous: results are on the host when the call returns. dl/d/du are not
+ * modified. solver: 0 thomas, 1 bfb, 2 cr.
+ * ---------------------------------------------------------------------- */
+typedef struct ekat_b200_pipeline ekat_b200_pipeline;
+int ekat_b200_pipeline_create(ekat_b200_pipeline** out, size_t device_bytes, int nslots);
+int ekat_b200_pipeline_destroy(ekat_b200_pipeline* p);
+/* totals since creation: bytes uploaded, bytes downloaded, chunks processed */
+int ekat_b200_pipeline_stats(ekat_b200_pipeline* p, uint64_t* h2d_bytes, uint64_t* d2h_bytes, uint64_t* chunks);
+int ekat_b200_tridiag_host_f64(ekat_b200_pipeline* p, int solver, const double* dl, const double* d,
+                               const double* du, double* X, int64_t ncol, int nlev, int nA, int nrhs,
+                               int64_t a_stride, int64_t x_stride, int layout);
+int ekat_b200_tridiag_host_f32(ekat_b200_pipeline* p, int solver, const float* dl, const float* d, const float* du,
+                               float* X, int64_t ncol, int nlev, int nA, int nrhs, int64_t a_stride,
+                               int64_t x_stride, int layout);
+int ekat_b200_lin_interp_host_f64(ekat_b200_pipeline* p, const double* x1, const double* x2, const double* y1,
+                                  double* y2, int64_t ncol, int km1, int km2, int64_t pitch1, int64_t pitch2,
+                                  int nfields, int64_t y1_fstride, int64_t y2_fstride);
+int ekat_b200_lin_interp_host_f32(ekat_b200_pipeline* p, const float* x1, const float* x2, const float* y1,
+                                  float* y2, int64_t ncol, int km1, int km2, int64_t pitch1, int64_t pitch2,
+                                  int nfields, int64_t y1_fstride, int64_t y2_fstride);
+
+/* device memory for the host adapters' own state (LinInterp's index map), so that the C++ headers
+ * need no CUDA headers: thin wrappers over cudaMalloc / cudaFree on the current device. */
+int ekat_b200_device_alloc(void** ptr, size_t bytes);
+int ekat_b200_device_free(void* ptr);
+
+/* ------------------------------------------------------------------------
+ * Introspection / tuning.
+ * ---------------------------------------------------------------------- */
+int ekat_b200_version(void);
+/* text of the last CUDA error seen by this thread inside the library ("" if none) */
+const char* ekat_b200_last_cuda_error(void);
+/* number of kernels this library has launched in this process (all threads) */
+uint64_t ekat_b200_launch_count(void);
+/* name of the last kernel variant chosen by the calling thread (for bench/profiles) */
+const char* ekat_b200_last_kernel(void);
+/* override launch heuristics (0 = automatic): columns per CTA and load-prefetch depth (levels)
+ * for the LEV_MAJOR thomas/bfb kernels. Thread-local. For tuning sweeps only. */
+void ekat_b200_set_tuning(int cols_per_cta, int prefetch_levels, int variant);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EKAT_B200_H */

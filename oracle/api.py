@@ -131,6 +131,18 @@ class CpuOracle:
         return (y2[0] if single else y2), indx
 
 
+    def lin_interp_raw(self, x1, x2, y1f, y2, indx, km1, km2, packn=1):
+        """The bare C call on caller-allocated, C-contiguous arrays (y1f/y2: [nfields,ncol,pitch]) -- for timing."""
+        ncol, nfields = x1.shape[0], y1f.shape[0]
+        s = _sfx(x1.dtype)
+        if self.kind == "port":
+            return getattr(self.lib, "ekat_oracle_lin_interp_" + s)(
+                _p(x1), _p(x2), _p(y1f), _p(y2), _p(indx), _i64(ncol), _int(km1), _int(km2),
+                _i64(x1.shape[1]), _i64(x2.shape[1]), _int(nfields))
+        return getattr(self.lib, "ekat_ref_lin_interp_" + s)(
+            _int(packn), _p(x1), _p(x2), _p(y1f), _p(y2), _p(indx), _i64(ncol), _int(km1), _int(km2), _int(nfields))
+
+
 _cache = {}
 
 

@@ -1,0 +1,92 @@
+// Compile-and-link test of the C++ host adapters against a Kokkos::View look-alike (oracle/standin),
+// plus the argument checks that need no GPU (run with --no-gpu), plus -- with a GPU and the device
+// pointers handed in by the harness (tests/test_gpu_adapters.py uses the .cu twin) -- nothing else.
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+
+#include <Kokkos_Core.hpp>  // the stand-in: only its View type is used
+
+#include "ekat_b200/ekat_lin_interp.hpp"
+#include "ekat_b200/ekat_tridiag.hpp"
+
+template <class S> using VR2 = Kokkos::View<S**, Kokkos::LayoutRight, Kokkos::MemoryUnmanaged>;
+template <class S> using VR3 = Kokkos::View<S***, Kokkos::LayoutRight, Kokkos::MemoryUnmanaged>;
+template <class S> using VL2 = Kokkos::View<S**, Kokkos::LayoutLeft, Kokkos::MemoryUnmanaged>;
+template <class S> using VL3 = Kokkos::View<S***, Kokkos::LayoutLeft, Kokkos::MemoryUnmanaged>;
+
+struct Pack16 {  // Pack<double,16> look-alike (src/pack/ekat_pack.hpp:219-232)
+  using scalar = double;
+  double d[16];
+};
+
+template <class F>
+static bool throws_invalid(F f) {
+  try {
+    f();
+  } catch (const std::invalid_argument&) {
+    return true;
+  } catch (...) {
+    return false;
+  }
+  return false;
+}
+
+int main(int argc, char** argv) {
+  const bool no_gpu = argc > 1 && !std::strcmp(argv[1], "--no-gpu");
+  using ekat::tridiag::Batched;
+  double* fake = reinterpret_cast<double*>(0x1000);  // never dereferenced in --no-gpu mode
+  float* fakef = reinterpret_cast<float*>(0x1000);
+  int bad = 0;
+
+  // empty batches are no-ops in every layout / rank / precision (instantiates all adapter templates)
+  {
+    VR2<double> a(fake, 0, 72), x(fake, 0, 72);
+    ekat::tridiag::thomas(Batched{}, a, a, a, x);
+    ekat::tridiag::bfb(Batched{}, a, a, a, x);
+    ekat::tridiag::cr(Batched{}, a, a, a, x);
+    VR3<double> a3(fake, 0, 72, 1), x3(fake, 0, 72, 10);
+    ekat::tridiag::thomas(Batched{}, a3, a3, a3, x3);
+    ekat::tridiag::bfb(Batched{}, a, a, a, x3);
+    VL2<float> al(fakef, 0, 72), xl(fakef, 0, 72);
+    ekat::tridiag::thomas(Batched{}, al, al, al, xl);
+    VL3<float> al3(fakef, 0, 72, 4), xl3(fakef, 0, 72, 4);
+    ekat::tridiag::cr(Batched{nullptr, true}, al3, al3, al3, xl3);
+    VR3<Pack16> ap(reinterpret_cast<Pack16*>(fake), 0, 72, 1), xp(reinterpret_cast<Pack16*>(fake), 0, 72, 1);
+    ekat::tridiag::thomas(Batched{}, ap, ap, ap, xp);
+  }
+  // the reference's asserts become std::invalid_argument
+  {
+    VR2<double> a(fake, 8, 72), x(fake, 8, 71), x9(fake, 9, 72);
+    bad += !throws_invalid([&] { ekat::tridiag::thomas(Batched{}, a, a, a, x); });   // nrow differs (:328-330)
+    bad += !throws_invalid([&] { ekat::tridiag::bfb(Batched{}, a, a, a, x9); });     // column count differs
+    VR3<double> a2(fake, 8, 72, 2), x3(fake, 8, 72, 3);
+    bad += !throws_invalid([&] { ekat::tridiag::cr(Batched{}, a2, a2, a2, x3); });   // nA not in {1, nrhs}
+    VL2<double> xl(fake, 8, 72);
+    bad += !throws_invalid([&] { ekat::tridiag::thomas(Batched{}, a, a, a, xl); });  // mixed layouts
+  }
+  // LinInterp: ctor / getters / extents (lin_interp_test.cpp:47-92 runs the API on an empty problem)
+  {
+    ekat::b200::LinInterp<double, 16> li(0, 0, 0);
+    VR2<const double> x1(fake, 0, 0), x2(fake, 0, 0), y1(fake, 0, 0);
+    VR2<double> y2(fake, 0, 0);
+    li.setup(x1, x2);
+    li.lin_interp(x1, x2, y1, y2);
+    li.setup_and_interp(x1, x2, y1, y2);
+    ekat::b200::LinInterp<float, 1> lf(0, 72, 128);
+    if (lf.km1_pack() != 72 || lf.km2_pack() != 128) ++bad;
+    ekat::b200::LinInterp<double, 16> lp(0, 72, 128);
+    if (lp.km1_pack() != 5 || lp.km2_pack() != 8) ++bad;
+    VR2<const Pack16> xp(reinterpret_cast<const Pack16*>(fake), 0, 5), xq(reinterpret_cast<const Pack16*>(fake), 0, 8);
+    lp.setup(xp, xq);
+    VR2<const double> wrong(fake, 0, 72);  // scalar view must be npack*N = 80 wide
+    bad += !throws_invalid([&] { lp.setup(wrong, xq); });
+  }
+  if (bad) {
+    std::printf("adapter argument checks FAILED (%d)\n", bad);
+    return 1;
+  }
+  std::printf("adapter argument checks ok\n");
+  (void)no_gpu;
+  return 0;
+}

@@ -1,0 +1,195 @@
+"""GPU parity tests proper: every tridiagonal entry point of the C ABI (called through ekat_b200.tridiag's ctypes
+face) against the CPU oracle on identical inputs.
+
+  bfb, cr : bit-exact against the reference arithmetic (oracle port; == oracle/_ref, see test_oracle.py)
+  thomas  : max|a-b|/max|a| <= 1e-13 (f64) / 1e-5 (f32)           [north_star tolerances]
+Shapes follow the reference's property test (tests/algorithm/tridiag_tests_correctness.cpp:403-484): all its nrow
+values, single / shared-A multi / per-rhs-A right-hand sides, plus ragged column counts, padded pitches and
+strided batches for both layouts.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import NROWS, a_to_lev, bits_equal, eps, rel_diff, tol, x_from_lev, x_to_lev
+import ekat_b200
+from ekat_b200 import tridiag as T
+
+pytestmark = pytest.mark.gpu
+DT = {"f64": (np.float64, torch.float64), "f32": (np.float32, torch.float32)}
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+REFNAME = {"thomas": "thomas", "bfb": "bfb", "cr": "cr"}
+
+
+def run_gpu(solver, A, X, layout, dev, clobber=False, pad=0):
+    """A[ncol,3,nrow,nA], X[ncol,nrow,nrhs] (numpy, reference layout) -> solution in the same layout (+ clobbered A)."""
+    fn = getattr(T, solver)
+    ncol = A.shape[0]
+    if layout == ekat_b200.LEV_MAJOR:
+        dl, d, du = (torch.from_numpy(np.pad(a, ((0, 0), (0, 0), (0, pad)))).to(dev) for a in a_to_lev(A))
+        x = torch.from_numpy(np.pad(x_to_lev(X), ((0, 0), (0, 0), (0, pad)))).to(dev)
+        fn(dl, d, du, x, layout=layout, clobber=clobber, ncol=ncol)
+        torch.cuda.synchronize()
+        Aout = np.stack([t.cpu().numpy()[:, :, :ncol].transpose(2, 1, 0) for t in (dl, d, du)], axis=1)
+        return x_from_lev(x.cpu().numpy()[:, :, :ncol]), np.ascontiguousarray(Aout)
+    At = torch.from_numpy(A).to(dev)
+    Xt = torch.from_numpy(X).to(dev)
+    fn(At[:, 0], At[:, 1], At[:, 2], Xt, layout=layout, clobber=clobber)  # strided slices of A[ncol,3,nrow,nA]
+    torch.cuda.synchronize()
+    return Xt.cpu().numpy(), At.cpu().numpy()
+
+
+def check(solver, got, want, dtype, ctx):
+    if solver in ("bfb", "cr"):
+        assert bits_equal(got, want), f"{solver} not bit-exact: {ctx} rel={rel_diff(want, got):.3e}"
+    else:
+        assert rel_diff(want, got) <= tol(dtype), f"thomas off by {rel_diff(want, got):.3e}: {ctx}"
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+@pytest.mark.parametrize("solver", ["thomas", "bfb", "cr"])
+@pytest.mark.parametrize("layout", [ekat_b200.LEV_MAJOR, ekat_b200.COL_MAJOR])
+def test_parity_reference_shapes(cuda, port, dt, solver, layout):
+    npdt, _ = DT[dt]
+    for nrow in NROWS:
+        for nrhs, nA in [(1, 1), (5, 1), (5, 5), (13, 1)]:
+            ncol = 37  # ragged against every tile width
+            A, B = port.fill_tridiag(npdt, ncol, nrow, nA, nrhs, col0=3)
+            want = port.tridiag(REFNAME[solver], A.copy(), B.copy())
+            got, Aout = run_gpu(solver, A, B, layout, cuda, pad=3 if layout == ekat_b200.LEV_MAJOR else 0)
+            check(solver, got, want, npdt, (dt, layout, nrow, nrhs, nA))
+            assert bits_equal(Aout, A), "dl/d/du must be untouched without CLOBBER_DIAGS"
+            assert port.residual(A, B, got) <= 50 * eps(npdt)  # the reference's own acceptance test
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+@pytest.mark.parametrize("layout", [ekat_b200.LEV_MAJOR, ekat_b200.COL_MAJOR])
+def test_long_columns_2048(cuda, port, dt, layout):
+    """nrow = 2048 (the reference's NDEBUG-only case, :410-414): few columns, many levels."""
+    npdt, _ = DT[dt]
+    for solver in ("thomas", "bfb", "cr"):
+        for nrhs, nA in [(1, 1), (3, 1)]:
+            A, B = port.fill_tridiag(npdt, 5, 2048, nA, nrhs, col0=1)
+            want = port.tridiag(solver, A.copy(), B.copy())
+            got, _ = run_gpu(solver, A, B, layout, cuda)
+            check(solver, got, want, npdt, (dt, layout, solver, nrhs))
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+def test_golden_fixture(cuda, dt):
+    """Against the committed outputs of the unchanged reference headers (tests/golden, oracle/gen_golden.py)."""
+    npdt, tdt = DT[dt]
+    g = np.load(os.path.join(GOLD, "tridiag.npz"), allow_pickle=True)
+    for gdt, nrow, nrhs, nA, ncol, col0 in g["meta"]:
+        if gdt != dt:
+            continue
+        for layout in (ekat_b200.LEV_MAJOR, ekat_b200.COL_MAJOR):
+            dl, d, du, X = T.fill(tdt, ncol, nrow, nA, nrhs, layout=layout, col0=col0, device=cuda)
+            for solver in ("bfb", "cr", "thomas"):
+                x = X.clone()
+                getattr(T, solver)(dl, d, du, x, layout=layout)
+                got = x.cpu().numpy()
+                got = x_from_lev(got) if layout == ekat_b200.LEV_MAJOR else got
+                check(solver, got, g[f"{dt}_{solver}_n{nrow}_r{nrhs}_a{nA}"], npdt, ("golden", layout, nrow, nrhs, nA))
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+@pytest.mark.parametrize("layout", [ekat_b200.LEV_MAJOR, ekat_b200.COL_MAJOR])
+def test_clobber_diags_matches_reference_side_effect(cuda, port, dt, layout):
+    """With CLOBBER_DIAGS bfb leaves multipliers in dl and pivots in d, bit for bit as the reference does
+    (ekat_tridiag.hpp:299-302); du is unchanged."""
+    npdt, _ = DT[dt]
+    for nrhs, nA in [(1, 1), (4, 1), (4, 4)]:
+        A, B = port.fill_tridiag(npdt, 45, 72, nA, nrhs, col0=9)
+        Aref, Xref = A.copy(), B.copy()
+        port.tridiag("bfb", Aref, Xref)
+        got, Aout = run_gpu("bfb", A, B, layout, cuda, clobber=True)
+        assert bits_equal(got, Xref)
+        assert bits_equal(Aout[:, 0, 1:], Aref[:, 0, 1:]), "dl multipliers"
+        assert bits_equal(Aout[:, 1], Aref[:, 1]), "d pivots"
+        assert bits_equal(Aout[:, 2], A[:, 2]), "du untouched"
+        # thomas with clobber: pivots agree to tolerance with the serial reference (:221)
+        Aref2, Xref2 = A.copy(), B.copy()
+        port.tridiag("thomas", Aref2, Xref2)
+        got2, Aout2 = run_gpu("thomas", A, B, layout, cuda, clobber=True)
+        assert rel_diff(Xref2, got2) <= tol(npdt)
+        if layout == ekat_b200.LEV_MAJOR:
+            assert rel_diff(Aref2[:, 1], Aout2[:, 1]) <= tol(npdt)
+
+
+def test_tuning_variants_agree(cuda, port):
+    """Every launch geometry / prefetch depth gives the same bits (bfb) -- results are independent of the
+    'team' shape, as the reference's are of its (thread, vector) parameterisation (:375-390)."""
+    from ekat_b200._lib import lib
+    A, B = port.fill_tridiag(np.float64, 333, 72, 1, 1, col0=0)
+    want = port.tridiag("bfb", A.copy(), B.copy())
+    try:
+        for cols in (8, 16, 32, 64, 96):
+            for pf in (4, 8, 16):
+                lib().ekat_b200_set_tuning(cols, pf, 0)
+                got, _ = run_gpu("bfb", A, B, ekat_b200.LEV_MAJOR, cuda)
+                assert bits_equal(got, want), (cols, pf)
+        lib().ekat_b200_set_tuning(0, 0, 2)  # force the tile kernel on level-major data
+        got, _ = run_gpu("bfb", A, B, ekat_b200.LEV_MAJOR, cuda)
+        assert bits_equal(got, want)
+        for cols in (1, 3, 8, 21):
+            lib().ekat_b200_set_tuning(cols, 0, 0)
+            for layout in (ekat_b200.LEV_MAJOR, ekat_b200.COL_MAJOR):
+                got, _ = run_gpu("cr", A, B, layout, cuda)
+                assert bits_equal(got, port.tridiag("cr", A.copy(), B.copy())), cols
+    finally:
+        lib().ekat_b200_set_tuning(0, 0, 0)
+
+
+def test_edge_cases(cuda, port):
+    dev = cuda
+    # ncol == 0 is a silent no-op; shapes are still validated
+    e = torch.empty((72, 0), dtype=torch.float64, device=dev)
+    T.bfb(e, e, e, e.clone())
+    # one column, one level
+    A, B = port.fill_tridiag(np.float64, 1, 1, 1, 1)
+    for s in ("thomas", "bfb", "cr"):
+        got, _ = run_gpu(s, A, B, ekat_b200.LEV_MAJOR, dev)
+        assert got[0, 0, 0] == B[0, 0, 0] / A[0, 1, 0, 0]
+    # wrong shapes raise before any launch
+    a = torch.zeros((72, 8), dtype=torch.float64, device=dev)
+    with pytest.raises(ValueError):
+        T.bfb(a, a, a, torch.zeros((71, 8), dtype=torch.float64, device=dev))
+    with pytest.raises(ValueError):
+        T.bfb(a, a, a, torch.zeros((72, 8), dtype=torch.float32, device=dev))
+    with pytest.raises(ValueError):
+        T.bfb(a.cpu(), a.cpu(), a.cpu(), a.cpu())  # no CPU path
+    # a column too long for on-chip staging is reported, not silently mis-solved
+    big = torch.ones((3, 40000), dtype=torch.float64, device=dev)
+    with pytest.raises(ekat_b200.EkatB200Error) as ei:
+        T.cr(big, big, big, big.clone(), layout=ekat_b200.COL_MAJOR)
+    assert ei.value.rc == -4
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+def test_full_size_configs_properties(cuda, port, dt):
+    """BASELINE sizes, checked through size-independent properties: the reference's residual test on every
+    column (device reduction), bit-equality of a sampled slab with the oracle, and partition-invariance of the
+    checksum (sum of per-shard checksums == whole-batch checksum)."""
+    npdt, tdt = DT[dt]
+    for ncol, nlev in [(21600, 72), (345600, 128)]:  # C1 and C3
+        dl, d, du, B = T.fill(tdt, ncol, nlev, 1, 1, device=cuda)
+        for solver in ("thomas", "bfb", "cr"):
+            X = B.clone()
+            getattr(T, solver)(dl, d, du, X)
+            res = float(T.residual(dl, d, du, B, X).item())
+            assert res <= 50 * eps(npdt), (solver, ncol, res)
+            # sampled slab vs oracle (columns straddling the 32768 seed wrap for the big case)
+            c0 = min(ncol - 64, 32768 - 32)
+            A_h, B_h = port.fill_tridiag(npdt, 64, nlev, 1, 1, col0=c0)
+            want = port.tridiag(solver, A_h.copy(), B_h.copy())
+            got = x_from_lev(X[:, :, c0:c0 + 64].cpu().numpy())
+            check(solver, got, want, npdt, (solver, ncol))
+            # checksum is associative over any column partition
+            whole = int(T.checksum(X).item())
+            parts = torch.zeros(1, dtype=torch.int64, device=cuda)
+            for lo, hi in [(0, ncol // 3), (ncol // 3, ncol // 2 + 7), (ncol // 2 + 7, ncol)]:
+                T.checksum(X[:, :, lo:hi], out=parts)
+            assert whole == int(parts.item())

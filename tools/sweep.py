@@ -1,0 +1,155 @@
+"""Tuning / measurement sweep for the kernels (run on the GPU box):  python tools/sweep.py [what ...]
+Prints one JSON line per measurement: kernel, shape, tuning, ms, col-lev/s, algorithmic GB/s, fraction of the
+measured HBM peak. CUDA-event timing, 3 warm-ups, inputs restored outside the timed region; L2 is flushed
+between iterations for working sets that would fit in it."""
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import ekat_b200  # noqa: E402
+from ekat_b200 import tridiag as T  # noqa: E402
+from ekat_b200._lib import lib  # noqa: E402
+from ekat_b200.lin_interp import LinInterp, fill as li_fill, tridiag_lin_interp  # noqa: E402
+
+dev = torch.device("cuda:0")
+PEAK = 6551.0
+try:
+    PEAK = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+except Exception:
+    pass
+_flush = None
+
+
+def flush_l2():
+    global _flush
+    if _flush is None:
+        _flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    _flush.zero_()
+
+
+def timeit(fn, restore=None, iters=10, flush=False):
+    for _ in range(3):
+        if restore:
+            restore()
+        fn()
+    torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(iters):
+        if restore:
+            restore()
+        if flush:
+            flush_l2()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        tot += a.elapsed_time(b)
+    return tot / iters
+
+
+def report(**kw):
+    print(json.dumps(kw), flush=True)
+
+
+def tridiag_case(solver, dt, ncol, nlev, nA=1, nrhs=1, layout=ekat_b200.LEV_MAJOR, tunings=((0, 0, 0),), tag=""):
+    tdt = torch.float64 if dt == "f64" else torch.float32
+    w = 8 if dt == "f64" else 4
+    dl, d, du, B = T.fill(tdt, ncol, nlev, nA, nrhs, layout=layout, device=dev)
+    X = B.clone()
+    alg = (3 * nA + 2 * nrhs) * nlev * w * ncol
+    small = alg < (200 << 20)
+    for tu in tunings:
+        lib().ekat_b200_set_tuning(*tu)
+        try:
+            ms = timeit(lambda: getattr(T, solver)(dl, d, du, X, layout=layout), restore=lambda: X.copy_(B), flush=small)
+        except Exception as e:  # noqa: BLE001
+            report(kernel=solver, dt=dt, ncol=ncol, nlev=nlev, nA=nA, nrhs=nrhs, layout=layout, tuning=tu, error=str(e))
+            continue
+        finally:
+            lib().ekat_b200_set_tuning(0, 0, 0)
+        report(kernel=solver, variant=lib().ekat_b200_last_kernel().decode(), dt=dt, ncol=ncol, nlev=nlev, nA=nA, nrhs=nrhs,
+               layout="lev" if layout else "col", tuning=tu, ms=round(ms, 4), col_lev_per_s=ncol * nlev / ms * 1e3,
+               gbs=round(alg / ms / 1e6, 1), frac=round(alg / ms / 1e6 / PEAK, 3), l2_flushed=small, tag=tag)
+
+
+def li_case(dt, ncol, km1, km2, N=1, nf=1, tunings=((0, 0, 0),)):
+    tdt = torch.float64 if dt == "f64" else torch.float32
+    w = 8 if dt == "f64" else 4
+    x1, y1, x2 = li_fill(tdt, ncol, km1, km2, N, device=dev)
+    li = LinInterp(ncol, km1, km2, tdt, N, device=dev)
+    y1f = y1.unsqueeze(0).repeat(nf, 1, 1).contiguous()
+    y2 = torch.zeros((nf, ncol, li.pitch2), dtype=tdt, device=dev)
+    alg = (km1 + km2) * (1 + nf) * w * ncol
+    small = alg < (200 << 20)
+    for tu in tunings:
+        lib().ekat_b200_set_tuning(*tu)
+        ms = timeit(lambda: li.run(x1, x2, y1f, y2), flush=small)
+        lib().ekat_b200_set_tuning(0, 0, 0)
+        report(kernel="lin_interp", dt=dt, ncol=ncol, km1=km1, km2=km2, pack=N, nfields=nf, tuning=tu, ms=round(ms, 4),
+               col_lev_per_s=ncol * km2 / ms * 1e3, gbs=round(alg / ms / 1e6, 1), frac=round(alg / ms / 1e6 / PEAK, 3),
+               l2_flushed=small)
+    ms = timeit(lambda: (li.setup(x1, x2), li.lin_interp(x1, x2, y1f, y2)), flush=small)
+    report(kernel="lin_interp setup+apply", dt=dt, ncol=ncol, km1=km1, km2=km2, pack=N, nfields=nf, ms=round(ms, 4),
+           gbs=round(alg / ms / 1e6, 1), frac=round(alg / ms / 1e6 / PEAK, 3))
+
+
+def fused_case(dt, ncol, nlev, km2, nrhs, tunings=((0, 0, 0),)):
+    tdt = torch.float64 if dt == "f64" else torch.float32
+    w = 8 if dt == "f64" else 4
+    dl, d, du, B = T.fill(tdt, ncol, nlev, 1, nrhs, device=dev)
+    x1, _, x2 = li_fill(tdt, ncol, nlev, km2, 1, device=dev, lev_major=True)
+    Y2 = torch.zeros((nrhs, km2, ncol), dtype=tdt, device=dev)
+    alg = ((3 + nrhs + 1) * nlev + (1 + nrhs) * km2) * w * ncol
+    for tu in tunings:
+        lib().ekat_b200_set_tuning(*tu)
+        ms = timeit(lambda: tridiag_lin_interp(dl[0], d[0], du[0], B, x1, x2, Y2))
+        lib().ekat_b200_set_tuning(0, 0, 0)
+        report(kernel="tridiag_lin_interp", dt=dt, ncol=ncol, nlev=nlev, km2=km2, nrhs=nrhs, tuning=tu, ms=round(ms, 4),
+               col_lev_per_s=ncol * nlev / ms * 1e3, gbs=round(alg / ms / 1e6, 1), frac=round(alg / ms / 1e6 / PEAK, 3))
+
+
+def copy_peak():
+    n = 1 << 30
+    a = torch.empty(n, dtype=torch.uint8, device=dev)
+    b = torch.empty(n, dtype=torch.uint8, device=dev)
+    ms = timeit(lambda: b.copy_(a))
+    report(kernel="torch copy 1 GiB", ms=round(ms, 4), gbs=round(2 * n / ms / 1e6, 1))
+
+
+if __name__ == "__main__":
+    what = sys.argv[1:] or ["peak", "c3", "c1", "li", "multi", "col", "fused"]
+    if "peak" in what:
+        copy_peak()
+    if "c3" in what:
+        grid = [(t, p, 0) for t in (16, 32, 64, 96, 112) for p in (4, 8, 16)]
+        for dt in ("f64", "f32"):
+            for s in ("thomas", "bfb"):
+                tridiag_case(s, dt, 345600, 128, tunings=grid)
+            tridiag_case("cr", dt, 345600, 128, tunings=[(0, 0, 0), (8, 0, 0), (16, 0, 0), (32, 0, 0)])
+    if "c1" in what:
+        for s in ("thomas", "bfb", "cr"):
+            tridiag_case(s, "f64", 21600, 72, tunings=[(0, 0, 0), (16, 8, 0), (32, 4, 0), (32, 16, 0), (64, 8, 0)])
+    if "li" in what:
+        li_case("f64", 21600, 72, 128, 1, tunings=[(0, 0, 0), (0, 0, 1), (8, 0, 0), (32, 0, 0)])
+        li_case("f64", 21600, 72, 128, 16)
+        li_case("f64", 345600, 72, 128, 1, tunings=[(0, 0, 0), (0, 0, 1), (4, 0, 0), (8, 0, 0), (16, 0, 0), (32, 0, 0), (64, 0, 0)])
+        li_case("f64", 345600, 128, 128, 1)
+        li_case("f32", 345600, 72, 128, 1)
+        li_case("f64", 345600, 72, 128, 1, nf=4)
+    if "multi" in what:
+        for s in ("thomas", "bfb"):
+            tridiag_case(s, "f64", 345600, 128, 1, 10, tunings=[(0, 0, 0), (8, 0, 0), (16, 0, 0)])
+            tridiag_case(s, "f64", 345600, 128, 10, 10)
+        tridiag_case("cr", "f64", 100000, 128, 1, 10)
+    if "col" in what:
+        for s in ("thomas", "bfb", "cr"):
+            tridiag_case(s, "f64", 345600, 128, layout=ekat_b200.COL_MAJOR, tunings=[(0, 0, 0), (8, 0, 0), (32, 0, 0)])
+        tridiag_case("cr", "f64", 64, 2048, layout=ekat_b200.COL_MAJOR)
+        tridiag_case("cr", "f64", 2048, 128, nrhs=43, nA=43, layout=ekat_b200.COL_MAJOR, tag="reference perf default")
+    if "fused" in what:
+        fused_case("f64", 393216, 128, 128, 10, tunings=[(0, 0, 0), (8, 0, 0)])
