@@ -124,9 +124,9 @@ def cpu_run(steps, warmup, budget_s=25.0, sample_cols=None):
         step()
     tt = tl = 0.0
     for _ in range(reps):
-        a, b = step()
-        tt += a
-        tl += b
+        dt_tri, dt_li = step()
+        tt += dt_tri
+        tl += dt_li
     units = reps * ncol * (NLEV + KM2)
     return {"value": units / (tt + tl), "unit": "column-levels/s", "cores": cores, "kind": kind,
             "sample": f"{ncol} columns x 128 levels f64: thomas (serial form) + LinInterp 128->128, {reps} timed passes, "

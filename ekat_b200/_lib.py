@@ -33,6 +33,8 @@ for _t in ("f64", "f32"):
 _SIGS["ekat_b200_pipeline_create"] = [ctypes.POINTER(vp), ctypes.c_size_t, cint]
 _SIGS["ekat_b200_pipeline_destroy"] = [vp]
 _SIGS["ekat_b200_pipeline_stats"] = [vp, ctypes.POINTER(u64), ctypes.POINTER(u64), ctypes.POINTER(u64)]
+_SIGS["ekat_b200_selftest_div_f64"] = [u64, u64, cint, vp, vp]
+_SIGS["ekat_b200_selftest_div_f32"] = [u64, u64, cint, vp, vp]
 _SIGS["ekat_b200_device_alloc"] = [ctypes.POINTER(vp), ctypes.c_size_t]
 _SIGS["ekat_b200_device_free"] = [vp]
 _SIGS["ekat_b200_version"] = []

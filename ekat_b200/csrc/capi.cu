@@ -38,6 +38,9 @@ template <typename R>
 int residual(const R* dl, const R* d, const R* du, const R* B, const R* X, int64_t ncol, int nlev, int nA, int nrhs,
              int64_t pitch, double* out, cudaStream_t st);
 
+template <typename R>
+int selftest_div(uint64_t n, uint64_t seed, int mode, uint64_t* mismatches, cudaStream_t st);
+
 // ------------------------------------------------------------------ per-thread / process state
 static std::atomic<uint64_t> g_launches{0};
 static thread_local char t_err[256] = "";
@@ -204,6 +207,13 @@ DEF_FUSED(float, f32)
   }
 DEF_UTIL(double, f64)
 DEF_UTIL(float, f32)
+
+int ekat_b200_selftest_div_f64(uint64_t n, uint64_t seed, int mode, uint64_t* mismatches, ekat_b200_stream_t s) {
+  return mismatches ? selftest_div<double>(n, seed, mode, mismatches, ST(s)) : EKAT_B200_ERR_INVALID;
+}
+int ekat_b200_selftest_div_f32(uint64_t n, uint64_t seed, int mode, uint64_t* mismatches, ekat_b200_stream_t s) {
+  return mismatches ? selftest_div<float>(n, seed, mode, mismatches, ST(s)) : EKAT_B200_ERR_INVALID;
+}
 
 int ekat_b200_device_alloc(void** ptr, size_t bytes) {
   if (!ptr) return EKAT_B200_ERR_INVALID;

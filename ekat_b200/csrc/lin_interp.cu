@@ -19,6 +19,9 @@
 //     y2  = y1[k1ph] - y1[k1];  y2 *= x2 - x1[k1];  y2 /= x1[k1ph] - x1[k1];  y2 += y1[k1]
 // so results are bit-identical to the reference at -ffp-contract=off, for any Pack size
 // (pack padding is skipped: only the first km1 / km2 entries of a row are touched as data).
+#include <cstdio>
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace ekb {
@@ -235,6 +238,9 @@ int lin_interp(int mode, const R* x1, const R* x2, const R* y1, R* y2, int* indx
   const unsigned grid = (unsigned)tmin<int64_t>(ntiles, (int64_t)kNumSms * per_sm);
   int rc;
   const char* name;
+  if (getenv("EKAT_B200_DEBUG"))
+    fprintf(stderr, "[ekat_b200] lin_interp mode=%d ncol=%lld km1=%d km2=%d p1=%lld p2=%lld nf=%d CB=%d smem=%zu grid=%u tma=%d\n",
+            mode, (long long)ncol, km1, km2, (long long)pitch1, (long long)pitch2, nf, CB, smem, grid, (int)use_tma);
   if (mode == LI_FUSED) {
     auto k = k_lin_interp<R, LI_FUSED>;
     if ((rc = allow_smem(k, smem))) return rc;

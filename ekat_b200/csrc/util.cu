@@ -193,6 +193,50 @@ __global__ void k_residual(const R* __restrict__ dl, const R* __restrict__ d, co
   if ((threadIdx.x & 31) == 0) atomicMax(out, (unsigned long long)__double_as_longlong(worst));  // >= 0: bit order == value order
 }
 
+// ------------------------------------------------------------------------ self test
+// x_div_pipelined (reciprocal hoisted, common.cuh) against the compiler's IEEE division on random operands:
+// mode 0 = random bit patterns (every exponent, denormals, infinities, NaNs excluded from the count when both
+// results are NaN), mode 1 = operands in the well-scaled range the solvers see. Counts bitwise mismatches.
+template <typename R> struct DivRef;
+template <> struct DivRef<double> {
+  using U = unsigned long long;
+  static __device__ double make(uint64_t b) { return __longlong_as_double((long long)b); }
+  static __device__ U bits(double v) { return (U)__double_as_longlong(v); }
+  static __device__ double ref(double a, double b) { return __ddiv_rn(a, b); }
+};
+template <> struct DivRef<float> {
+  using U = unsigned;
+  static __device__ float make(uint64_t b) { return __uint_as_float((unsigned)(b >> 16)); }
+  static __device__ U bits(float v) { return __float_as_uint(v); }
+  static __device__ float ref(float a, float b) { return __fdiv_rn(a, b); }
+};
+template <typename R>
+__global__ void k_selftest_div(uint64_t n, uint64_t seed, int mode, unsigned long long* mismatches) {
+  unsigned long long bad = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t ra = splitmix64(seed + 2 * i), rb = splitmix64(seed + 2 * i + 1);
+    R a, b;
+    if (mode == 0) {
+      a = DivRef<R>::make(ra);
+      b = DivRef<R>::make(rb);
+    } else {
+      a = (R)(((double)(ra >> 11) * (1.0 / 9007199254740992.0) - 0.5) * 200.0);
+      b = (R)(((double)(rb >> 11) * (1.0 / 9007199254740992.0) + 0.01) * ((rb & 1) ? 60.0 : -60.0));
+    }
+    const R q = x_div_pipelined(a, b), w = DivRef<R>::ref(a, b);
+    if (DivRef<R>::bits(q) != DivRef<R>::bits(w) && !(q != q && w != w)) ++bad;
+  }
+  if (bad) atomicAdd(mismatches, bad);
+}
+template <typename R>
+int selftest_div(uint64_t n, uint64_t seed, int mode, uint64_t* mismatches, cudaStream_t st) {
+  k_selftest_div<R><<<kNumSms * 8, 256, 0, st>>>(n, seed, mode, reinterpret_cast<unsigned long long*>(mismatches));
+  note_launch("selftest_div");
+  return check_cuda(cudaGetLastError());
+}
+template int selftest_div<double>(uint64_t, uint64_t, int, uint64_t*, cudaStream_t);
+template int selftest_div<float>(uint64_t, uint64_t, int, uint64_t*, cudaStream_t);
+
 // ------------------------------------------------------------------------ host side
 template <typename R>
 int fill_tridiag(R* dl, R* d, R* du, R* X, int64_t ncol, int64_t col0, int nlev, int nA, int nrhs,

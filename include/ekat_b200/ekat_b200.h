@@ -235,6 +235,13 @@ int ekat_b200_lin_interp_host_f32(ekat_b200_pipeline* p, const float* x1, const 
                                   float* y2, int64_t ncol, int km1, int km2, int64_t pitch1, int64_t pitch2,
                                   int nfields, int64_t y1_fstride, int64_t y2_fstride);
 
+/* Self test of the bit-exact division used by bfb / cr / LinInterp (the IEEE divide with its reciprocal
+ * hoisted off the dependent chain, csrc/common.cuh) against the compiler's __ddiv_rn / __fdiv_rn on n random
+ * operand pairs: mode 0 = random bit patterns (all exponents, denormals, infinities), mode 1 = well-scaled
+ * operands. *mismatches (device uint64) += number of bitwise differences; 0 is the only acceptable answer. */
+int ekat_b200_selftest_div_f64(uint64_t n, uint64_t seed, int mode, uint64_t* mismatches, ekat_b200_stream_t s);
+int ekat_b200_selftest_div_f32(uint64_t n, uint64_t seed, int mode, uint64_t* mismatches, ekat_b200_stream_t s);
+
 /* device memory for the host adapters' own state (LinInterp's index map), so that the C++ headers
  * need no CUDA headers: thin wrappers over cudaMalloc / cudaFree on the current device. */
 int ekat_b200_device_alloc(void** ptr, size_t bytes);

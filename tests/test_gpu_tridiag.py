@@ -131,6 +131,11 @@ def test_tuning_variants_agree(cuda, port):
                 lib().ekat_b200_set_tuning(cols, pf, 0)
                 got, _ = run_gpu("bfb", A, B, ekat_b200.LEV_MAJOR, cuda)
                 assert bits_equal(got, want), (cols, pf)
+        for nA, nrhs in [(1, 1), (1, 3), (3, 3)]:  # scalar (unvectorised) cp.async path == vector path
+            A2, B2 = port.fill_tridiag(np.float64, 97, 33, nA, nrhs, col0=1)
+            lib().ekat_b200_set_tuning(0, 0, 3)
+            got, _ = run_gpu("bfb", A2, B2, ekat_b200.LEV_MAJOR, cuda)
+            assert bits_equal(got, port.tridiag("bfb", A2.copy(), B2.copy()))
         lib().ekat_b200_set_tuning(0, 0, 2)  # force the tile kernel on level-major data
         got, _ = run_gpu("bfb", A, B, ekat_b200.LEV_MAJOR, cuda)
         assert bits_equal(got, want)
@@ -143,6 +148,33 @@ def test_tuning_variants_agree(cuda, port):
         lib().ekat_b200_set_tuning(0, 0, 0)
 
 
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+def test_pipelined_division_is_ieee(cuda, dt):
+    """The divide used on the exact paths (reciprocal hoisted off the chain) equals __ddiv_rn / __fdiv_rn bit for
+    bit on 2^28 random bit patterns (all exponents, denormals, infinities) and 2^28 well-scaled operands."""
+    from ekat_b200._lib import lib, check
+    out = torch.zeros(1, dtype=torch.int64, device=cuda)
+    fn = getattr(lib(), f"ekat_b200_selftest_div_{dt}")
+    for mode in (0, 1):
+        check("selftest_div", fn(1 << 28, 12345 + mode, mode, out.data_ptr(), None))
+    torch.cuda.synchronize()
+    assert int(out.item()) == 0
+
+
+def test_odd_pitch_and_unaligned_views_use_the_scalar_path(cuda, port):
+    """Pitches / base pointers that are not 16-byte multiples cannot use 16-byte cp.async: same bits through the
+    8-byte path."""
+    A, B = port.fill_tridiag(np.float64, 37, 72, 1, 1, col0=2)
+    want = port.tridiag("bfb", A.copy(), B.copy())
+    for pad in (0, 2, 3):  # pitch 37 (odd), 39 (odd), 40 (even)
+        got, _ = run_gpu("bfb", A, B, ekat_b200.LEV_MAJOR, cuda, pad=pad)
+        assert bits_equal(got, want), pad
+    dl, d, du = (torch.from_numpy(np.pad(a, ((0, 0), (0, 0), (1, 2)))).to(cuda)[:, :, 1:] for a in a_to_lev(A))
+    x = torch.from_numpy(np.pad(x_to_lev(B), ((0, 0), (0, 0), (1, 2)))).to(cuda)[:, :, 1:]  # base pointer off by 8 bytes
+    T.bfb(dl, d, du, x, ncol=37)
+    assert bits_equal(x_from_lev(x.cpu().numpy()[:, :, :37]), want)
+
+
 def test_edge_cases(cuda, port):
     dev = cuda
     # ncol == 0 is a silent no-op; shapes are still validated
@@ -151,8 +183,12 @@ def test_edge_cases(cuda, port):
     # one column, one level
     A, B = port.fill_tridiag(np.float64, 1, 1, 1, 1)
     for s in ("thomas", "bfb", "cr"):
-        got, _ = run_gpu(s, A, B, ekat_b200.LEV_MAJOR, dev)
-        assert got[0, 0, 0] == B[0, 0, 0] / A[0, 1, 0, 0]
+        for layout in (ekat_b200.LEV_MAJOR, ekat_b200.COL_MAJOR):
+            got, _ = run_gpu(s, A, B, layout, dev)
+            if s == "thomas":
+                assert abs(got[0, 0, 0] - B[0, 0, 0] / A[0, 1, 0, 0]) <= 4 * eps(np.float64) * abs(got[0, 0, 0])
+            else:
+                assert got[0, 0, 0] == B[0, 0, 0] / A[0, 1, 0, 0]
     # wrong shapes raise before any launch
     a = torch.zeros((72, 8), dtype=torch.float64, device=dev)
     with pytest.raises(ValueError):

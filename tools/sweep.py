@@ -126,14 +126,14 @@ if __name__ == "__main__":
     if "peak" in what:
         copy_peak()
     if "c3" in what:
-        grid = [(t, p, 0) for t in (16, 32, 64, 96, 112) for p in (4, 8, 16)]
+        grid = [(t, p, 0) for t in (16, 32, 48, 64, 96) for p in (8, 16, 32)]
         for dt in ("f64", "f32"):
             for s in ("thomas", "bfb"):
                 tridiag_case(s, dt, 345600, 128, tunings=grid)
             tridiag_case("cr", dt, 345600, 128, tunings=[(0, 0, 0), (8, 0, 0), (16, 0, 0), (32, 0, 0)])
     if "c1" in what:
         for s in ("thomas", "bfb", "cr"):
-            tridiag_case(s, "f64", 21600, 72, tunings=[(0, 0, 0), (16, 8, 0), (32, 4, 0), (32, 16, 0), (64, 8, 0)])
+            tridiag_case(s, "f64", 21600, 72, tunings=[(0, 0, 0), (16, 8, 0), (16, 16, 0), (32, 8, 0), (64, 16, 0)])
     if "li" in what:
         li_case("f64", 21600, 72, 128, 1, tunings=[(0, 0, 0), (0, 0, 1), (8, 0, 0), (32, 0, 0)])
         li_case("f64", 21600, 72, 128, 16)
