@@ -30,6 +30,11 @@
 
 namespace ekb {
 
+// TMA-fed warp-per-tile kernel (tridiag_tma.cu); EKAT_B200_ERR_UNSUPPORTED if the operands do not qualify.
+template <typename R>
+int tridiag_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride,
+                int64_t x_stride, cudaStream_t stream);
+
 // ---------------------------------------------------------------------------------------
 // One matrix per rhs (nA == nrhs, incl. nrhs == 1): thread <-> (column group, blockIdx.y = matrix).
 // Planes ([nlev][T] vectors):  EXACT: P0 = d -> d', P1 = x -> x', P2 = du;  ring R0 = dl
@@ -315,6 +320,10 @@ template <typename R>
 int tridiag_levmajor(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nA, int nrhs,
                      int64_t a_stride, int64_t x_stride, unsigned flags, cudaStream_t stream) {
   const bool clobber = (flags & EKAT_B200_CLOBBER_DIAGS) != 0;
+  if (nA == nrhs && !clobber && tuning().variant == 0) {
+    const int rc = tridiag_tma<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
+    if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+  }
   constexpr int VEC = 16 / sizeof(R);
   const bool vec = tuning().variant != 3 && vec_ok<R>(dl, d, du, X, a_stride, x_stride);
   if (vec) {

@@ -1,0 +1,350 @@
+// tridiag_tma.cu -- batched Thomas / bfb on the native level-major layout, TMA-fed, one warp per 32-lane tile.
+//
+// Replaces the per-column loops around ekat::tridiag::thomas (reference src/algorithm/ekat_tridiag.hpp:323-381)
+// and ekat::tridiag::bfb (:292-320, :632-678) when one matrix belongs to one right-hand side (nA == nrhs).
+//
+// Why this shape (measured on B200, profiles/r01a_*): a column's forward sweep must stay on chip until its
+// back-substitution (2 words per level, 3 for bfb), so shared memory admits only ~100 f64 columns of 128 levels
+// per SM -- about three warps. The previous cp.async kernel spent those few warps on per-thread copy bookkeeping
+// (129 instructions per level and 16 active lanes per warp) and on the ~80-cycle divide chain of every level.
+// Here
+//  * a CTA is ONE full warp that owns a tile of W = 32*CPT adjacent columns; three such CTAs share an SM;
+//  * all operands arrive by 2D TMA tensor copies (cp.async.bulk.tensor, one instruction per LB levels x W
+//    columns per array, issued by lane 0, completion on mbarriers): x and du land directly in the planes the
+//    sweeps update in place, dl and d go through a small ring; no thread computes a global address;
+//  * solutions are written in place into the plane and leave by TMA tensor stores, LB levels at a time;
+//  * thomas uses the continuant ("ratio") form of the recurrence, which has no division on its dependent
+//    chain:   q[i] = d[i] q[i-1] - dl[i] du[i-1] q[i-2],   z[i] = x[i] q[i-1] - dl[i] z[i-1]
+//             c'[i] = du[i] q[i-1] / q[i],   y[i] = z[i] / q[i],   x[i] = y[i] - c'[i] x[i+1]
+//    (q[i] is the i-th leading minor; c', y are the classical Thomas intermediates). 1/q[i] is off the chain, so
+//    consecutive levels pipeline; every RN levels the state is renormalised to q = 1 (exactly the classical
+//    step) so that minors cannot overflow: pivots may range over 2^+-(1022/RN) (f64) / 2^+-(126/RN) (f32).
+//  * bfb keeps the reference's operation order with separately rounded * - / (bit-identical); its IEEE
+//    division has the reciprocal part hoisted off the back-substitution chain (common.cuh).
+// HBM traffic is the algorithmic minimum: read dl, d, du, x once, write x once.
+#include <cuda.h>
+
+#include "tridiag_lm_common.cuh"
+
+namespace ekb {
+
+// ------------------------------------------------------------------------------------------- tensor maps
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return (EncodeTiledFn) nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+// [nrows][pitch] array of R, of which the first ncol entries of a row are data; box = boxc columns x boxr rows.
+// Columns beyond ncol read as zero and are not written (TMA bounds handling).
+template <typename R>
+bool make_tensor_map_2d(CUtensorMap* m, const R* base, int64_t ncol, int64_t nrows, int64_t pitch, int boxc, int boxr) {
+  EncodeTiledFn enc = encode_fn();
+  if (!enc) return false;
+  const cuuint64_t dims[2] = {(cuuint64_t)ncol, (cuuint64_t)nrows};
+  const cuuint64_t strides[1] = {(cuuint64_t)pitch * sizeof(R)};
+  const cuuint32_t box[2] = {(cuuint32_t)boxc, (cuuint32_t)boxr};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUtensorMapDataType dt = sizeof(R) == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  return enc(m, dt, 2, const_cast<R*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+template bool make_tensor_map_2d<double>(CUtensorMap*, const double*, int64_t, int64_t, int64_t, int, int);
+template bool make_tensor_map_2d<float>(CUtensorMap*, const float*, int64_t, int64_t, int64_t, int, int);
+
+// Reciprocal for the ratio form: hardware seed (~2^-20) and one cubic Newton step (~2^-60 relative; eps is 2^-53).
+__device__ __forceinline__ double t_rcp(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double e = fma(-x, r, 1.0);
+  e = fma(e, e, e);
+  return fma(r, e, r);
+}
+__device__ __forceinline__ float t_rcp(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  const float e = fmaf(-x, r, 1.0f);
+  return fmaf(r, e, r);
+}
+
+constexpr int kLB = 8;  // levels per TMA box / mbarrier phase / unrolled chunk
+
+// ------------------------------------------------------------------------------------------- the kernel
+// grid = (column tiles, matrices); block = 32 threads. Lane l owns columns c0 + l*CPT .. +CPT-1.
+// Shared memory: [ring barriers NS][plane barriers nch] | planes [level][lane] | rings [stage][LB][lane].
+//   FAST : P0 = du -> c',  P1 = x -> y -> solution;            rings dl, d
+//   EXACT: P0 = d  -> d',  P1 = x -> x' -> solution,  P2 = du;  ring  dl
+template <typename R, bool EXACT, int CPT, int RN, int NS>
+__global__ void __launch_bounds__(32)
+k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
+              const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mx, R* __restrict__ X,
+              int64_t ncol, int nlev, int64_t x_stride, int pd) {
+  using V = Vec<R, CPT>;
+  constexpr int LB = kLB, W = 32 * CPT;
+  constexpr unsigned CHUNK_BYTES = LB * W * sizeof(R);
+  static_assert(LB % RN == 0, "renormalisation interval must divide the chunk");
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int lane = threadIdx.x;
+  const int nfull = nlev / LB, ntail = nlev - nfull * LB, nch = nfull + (ntail ? 1 : 0);
+
+  uint64_t* rbar = reinterpret_cast<uint64_t*>(smem_raw);
+  uint64_t* pbar = rbar + NS;
+  const size_t off = ((size_t)(NS + nch) * 8 + 127) & ~(size_t)127;
+  const size_t plane = (size_t)nch * LB * 32;  // V units
+  V* P0 = reinterpret_cast<V*>(smem_raw + off);
+  V* P1 = P0 + plane;
+  V* P2 = P1 + plane;                       // EXACT only
+  V* RA = EXACT ? P2 + plane : P1 + plane;  // dl ring
+  V* RB = RA + (size_t)NS * LB * 32;        // d ring (FAST only)
+
+  const int c0 = blockIdx.x * W;
+  const int row0 = blockIdx.y * nlev;
+
+  if (lane == 0) {
+    for (int s = 0; s < NS; ++s) mbar_init(&rbar[s], 1);
+    for (int k = 0; k < nch; ++k) mbar_init(&pbar[k], 1);
+    fence_mbar_init();
+  }
+  __syncwarp();
+
+  auto issue_ring = [&](int k) {
+    const int s = k % NS;
+    mbar_expect_tx(&rbar[s], (EXACT ? 1u : 2u) * CHUNK_BYTES);
+    tma_load_2d(RA + (size_t)s * LB * 32, &mdl, c0, row0 + k * LB, &rbar[s]);
+    if (!EXACT) tma_load_2d(RB + (size_t)s * LB * 32, &md, c0, row0 + k * LB, &rbar[s]);
+  };
+  auto issue_plane = [&](int k) {
+    const size_t o = (size_t)k * LB * 32;
+    mbar_expect_tx(&pbar[k], (EXACT ? 3u : 2u) * CHUNK_BYTES);
+    if (EXACT) {
+      tma_load_2d(P0 + o, &md, c0, row0 + k * LB, &pbar[k]);
+      tma_load_2d(P2 + o, &mdu, c0, row0 + k * LB, &pbar[k]);
+    } else {
+      tma_load_2d(P0 + o, &mdu, c0, row0 + k * LB, &pbar[k]);
+    }
+    tma_load_2d(P1 + o, &mx, c0, row0 + k * LB, &pbar[k]);
+  };
+  if (lane == 0) {
+    const int n0 = pd > NS ? pd : NS;
+    for (int k = 0; k < n0 && k < nch; ++k) {
+      if (k < NS) issue_ring(k);
+      if (k < pd) issue_plane(k);
+    }
+  }
+
+  // ---------------------------------------------------------------- forward sweep
+  // FAST state: q1 = q[i-1], q2 = q[i-2], z1 = z[i-1], cp = du[i-1].  EXACT state: q1 = d'[i-1], z1 = x'[i-1], cp = du[i-1].
+  R q1[CPT], q2[CPT], z1[CPT], cp[CPT];
+#pragma unroll
+  for (int j = 0; j < CPT; ++j) {
+    q1[j] = (R)1;
+    q2[j] = (R)0;
+    z1[j] = (R)0;
+    cp[j] = (R)0;
+  }
+  for (int k = 0; k < nch; ++k) {
+    const int s = k % NS;
+    mbar_wait(&rbar[s], (unsigned)(k / NS) & 1u);
+    mbar_wait(&pbar[k], 0u);
+    const V* ra = RA + (size_t)s * LB * 32 + lane;
+    const V* rb = RB + (size_t)s * LB * 32 + lane;
+    V* p0 = P0 + (size_t)k * LB * 32 + lane;
+    V* p1 = P1 + (size_t)k * LB * 32 + lane;
+    const V* p2 = P2 + (size_t)k * LB * 32 + lane;
+#pragma unroll
+    for (int u = 0; u < LB; ++u) {
+      V a = ra[u * 32], x = p1[u * 32], b, c;
+      if (EXACT) {
+        b = p0[u * 32];
+        c = p2[u * 32];
+      } else {
+        b = rb[u * 32];
+        c = p0[u * 32];
+      }
+      if (u == 0 && k == 0) {  // dl(0) is never used (ekat_tridiag.hpp:24-27) and may hold anything
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) a.v[j] = (R)0;
+      }
+      V o0, o1;
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) {
+        if (EXACT) {
+          const R m = x_div_pipelined(a.v[j], q1[j]);        // dl(i) /= d(i-1)            :300
+          const R dc = x_sub(b.v[j], x_mul(m, cp[j]));       // d(i) -= dl(i)*du(i-1)      :301
+          const R xc = x_sub(x.v[j], x_mul(m, z1[j]));       // X(i) -= dl(i)*X(i-1)       :315-316
+          o0.v[j] = dc;
+          o1.v[j] = xc;
+          q1[j] = dc;
+          z1[j] = xc;
+          cp[j] = c.v[j];
+        } else {
+          R q, z;
+          if (u % RN == 0) {  // state was renormalised: q[i-1] == 1, q2 = q[i-2]/q[i-1]
+            q = f_fma(-(a.v[j] * cp[j]), q2[j], b.v[j]);
+            z = f_fma(-a.v[j], z1[j], x.v[j]);
+          } else {
+            q = f_fma(b.v[j], q1[j], -((a.v[j] * cp[j]) * q2[j]));
+            z = f_fma(-a.v[j], z1[j], x.v[j] * q1[j]);
+          }
+          const R rq = t_rcp(q);
+          const R g = (u % RN == 0) ? rq : q1[j] * rq;  // q[i-1]/q[i] = 1/pivot
+          const R y = z * rq;
+          o0.v[j] = c.v[j] * g;
+          o1.v[j] = y;
+          if ((u + 1) % RN == 0) {  // renormalise: divide the state by q[i]
+            q2[j] = g;
+            z1[j] = y;
+            q1[j] = (R)1;
+          } else {
+            q2[j] = (u % RN == 0) ? (R)1 : q1[j];
+            q1[j] = q;
+            z1[j] = z;
+          }
+          cp[j] = c.v[j];
+        }
+      }
+      p0[u * 32] = o0;
+      p1[u * 32] = o1;
+    }
+    __syncwarp();  // every lane has read ring stage s
+    if (lane == 0) {
+      if (k + NS < nch) issue_ring(k + NS);
+      if (k + pd < nch) issue_plane(k + pd);
+    }
+  }
+  // du(nrow-1) is never used (:24-27): zero the coupling of the last level so the back-substitution is uniform
+  {
+    V zero;
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) zero.v[j] = (R)0;
+    (EXACT ? P2 : P0)[(size_t)(nlev - 1) * 32 + lane] = zero;
+  }
+
+  // ---------------------------------------------------------------- back substitution
+  R xv[CPT];
+#pragma unroll
+  for (int j = 0; j < CPT; ++j) xv[j] = (R)0;
+  auto step = [&](size_t i) {
+    const size_t e = i * 32 + lane;
+    const V y = P1[e], m0 = P0[e];
+    V o;
+    if (EXACT) {
+      const V ui = P2[e];
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) {
+        const R r = rcp_refined(m0.v[j]);  // off the x chain
+        xv[j] = div_given_rcp(x_sub(y.v[j], x_mul(ui.v[j], xv[j])), m0.v[j], r);  // :317-319
+        o.v[j] = xv[j];
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) {
+        xv[j] = f_fma(-m0.v[j], xv[j], y.v[j]);
+        o.v[j] = xv[j];
+      }
+    }
+    P1[e] = o;
+    return o;
+  };
+  if (ntail) {  // partial chunk: a tensor store would spill into the next matrix' rows -> plain stores
+    const int64_t col = (int64_t)c0 + lane * CPT;
+    for (int i = nlev - 1; i >= nfull * LB; --i) {
+      const V o = step((size_t)i);
+      R* g = X + (size_t)(row0 + i) * x_stride + col;
+#pragma unroll
+      for (int j = 0; j < CPT; ++j)
+        if (col + j < ncol) __stcs(g + j, o.v[j]);
+    }
+  }
+  for (int k = nfull - 1; k >= 0; --k) {
+#pragma unroll
+    for (int u = LB - 1; u >= 0; --u) step((size_t)k * LB + u);
+    fence_proxy_async();  // generic-proxy writes of this chunk -> visible to the TMA store
+    __syncwarp();
+    if (lane == 0) {
+      tma_store_2d(&mx, c0, row0 + k * LB, P1 + (size_t)k * LB * 32);
+      tma_store_commit();
+    }
+  }
+  if (lane == 0) tma_store_wait_read<0>();  // shared memory must outlive the stores' reads
+}
+
+// ------------------------------------------------------------------------------------------- host side
+template <typename R>
+struct TmaCfg;
+template <>
+struct TmaCfg<double> {
+  static constexpr int CPT = 1, RN = 8;
+};
+template <>
+struct TmaCfg<float> {
+  static constexpr int CPT = 2, RN = 2;
+};
+
+template <typename R, bool EXACT, int NS>
+static int launch_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
+                      int pd, size_t smem, cudaStream_t stream, const char* name) {
+  constexpr int CPT = TmaCfg<R>::CPT, RN = EXACT ? 1 : TmaCfg<R>::RN, W = 32 * CPT;
+  CUtensorMap mdl, md, mdu, mx;
+  const int64_t rows = (int64_t)nmat * nlev;
+  if (!make_tensor_map_2d<R>(&mdl, dl, ncol, rows, a_stride, W, kLB) || !make_tensor_map_2d<R>(&md, d, ncol, rows, a_stride, W, kLB) ||
+      !make_tensor_map_2d<R>(&mdu, du, ncol, rows, a_stride, W, kLB) || !make_tensor_map_2d<R>(&mx, X, ncol, rows, x_stride, W, kLB))
+    return EKAT_B200_ERR_UNSUPPORTED;
+  auto k = k_tridiag_tma<R, EXACT, CPT, RN, NS>;
+  int rc = allow_smem(k, smem);
+  if (rc) return rc;
+  dim3 grid((unsigned)((ncol + W - 1) / W), (unsigned)nmat);
+  k<<<grid, 32, smem, stream>>>(mdl, md, mdu, mx, X, ncol, nlev, x_stride, pd);
+  note_launch(name);
+  return check_cuda(cudaGetLastError());
+}
+
+// Returns EKAT_B200_ERR_UNSUPPORTED when the operands do not meet TMA's requirements (16-byte aligned bases and
+// pitches, column fits on chip, sizes within tensor-map limits); the caller then uses the cp.async kernels.
+template <typename R>
+int tridiag_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride,
+                int64_t x_stride, cudaStream_t stream) {
+  auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  if (!al(dl) || !al(d) || !al(du) || !al(X) || (a_stride * sizeof(R)) % 16 || (x_stride * sizeof(R)) % 16)
+    return EKAT_B200_ERR_UNSUPPORTED;
+  if (ncol >= (int64_t)1 << 31 || (int64_t)nmat * nlev >= (int64_t)1 << 31 || nmat > 65535) return EKAT_B200_ERR_UNSUPPORTED;
+  constexpr int CPT = TmaCfg<R>::CPT, W = 32 * CPT;
+  const Tuning tu = tuning();
+  const int nch = (nlev + kLB - 1) / kLB;
+  const size_t chunk = (size_t)kLB * W * sizeof(R);
+  const size_t bars = ((size_t)(8 + nch) * 8 + 127) & ~(size_t)127;
+  const size_t planes = (size_t)(exact ? 3 : 2) * nch * chunk;
+  const int nrings = exact ? 1 : 2;
+  // ring depth: 4 stages if that still leaves three CTAs per SM (or the column is short), else 2
+  int ns = 4;
+  const size_t third = (kMaxSmemPerCta + 1024) / 3 - 1024;  // per-CTA budget for 3 CTAs/SM (1 KB reserved per CTA)
+  if (bars + planes + (size_t)nrings * 4 * chunk > third && bars + planes + (size_t)nrings * 2 * chunk <= third) ns = 2;
+  if (tu.cols_per_cta == 2 || tu.cols_per_cta == 4) ns = tu.cols_per_cta;  // tuning override: ring stages
+  const size_t smem = bars + planes + (size_t)nrings * ns * chunk;
+  if (smem > kMaxSmemPerCta) return EKAT_B200_ERR_UNSUPPORTED;
+  int pd = tu.prefetch > 0 ? tu.prefetch : 6;  // plane chunks in flight ahead of the sweep
+  if (pd < 1) pd = 1;
+  const bool f64 = sizeof(R) == 8;
+  const char* name = exact ? (f64 ? "tridiag_tma<f64,bfb>" : "tridiag_tma<f32,bfb>")
+                           : (f64 ? "tridiag_tma<f64,thomas>" : "tridiag_tma<f32,thomas>");
+  if (exact)
+    return ns == 2 ? launch_tma<R, true, 2>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name)
+                   : launch_tma<R, true, 4>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name);
+  return ns == 2 ? launch_tma<R, false, 2>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name)
+                 : launch_tma<R, false, 4>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name);
+}
+
+template int tridiag_tma<double>(bool, double*, double*, double*, double*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
+template int tridiag_tma<float>(bool, float*, float*, float*, float*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
+
+}  // namespace ekb
