@@ -28,18 +28,24 @@ namespace ekb {
 
 enum LiMode { LI_FUSED = 0, LI_SETUP = 1, LI_APPLY = 2 };
 
-// upper_bound over x1[0..km1): first index with x1 > v (same predicate `v >= *it` as
-// ekat_upper_bound.hpp:37-48), select form instead of branches.
-template <typename R>
-__device__ __forceinline__ int bracket(const R* __restrict__ x1, int km1, R v) {
-  int lo = 0, n = km1;
-  while (n > 0) {
-    const int step = n >> 1, it = lo + step;
-    const bool ge = v >= x1[it];
-    lo = ge ? it + 1 : lo;
-    n = ge ? n - step - 1 : step;
+// upper_bound over sorted x1[0..km1): the number of entries <= v, found with the reference's predicate
+// `v >= *it` (ekat_upper_bound.hpp:37-48), so ties and NaNs resolve identically; then the reference's
+// "if (idx > 0) --idx" (:179-181). Branch-free: one probe picks the power-of-two window [0,P) or [km1-P,km1)
+// (P = bit_floor(km1)) that must contain the boundary, then log2(P) probes with halving steps and a last one --
+// each a shared-memory load, a compare and a predicated add. LOG2P > 0: unrolled for that window; 0: loop.
+template <typename R, int LOG2P>
+__device__ __forceinline__ int bracket(const R* __restrict__ x1, int km1, int P, R v) {
+  int pos = (km1 > P && v >= x1[km1 - P - 1]) ? km1 - P : 0;
+  if (LOG2P > 0) {
+#pragma unroll
+    for (int b = LOG2P - 1; b >= 0; --b)
+      if (v >= x1[pos + (1 << b) - 1]) pos += 1 << b;
+  } else {
+    for (int step = P >> 1; step >= 1; step >>= 1)
+      if (v >= x1[pos + step - 1]) pos += step;
   }
-  return lo > 0 ? lo - 1 : lo;  // :179-181
+  if (v >= x1[pos]) pos += 1;
+  return pos > 0 ? pos - 1 : pos;
 }
 
 struct LiArgs {
@@ -48,10 +54,10 @@ struct LiArgs {
   int* indx;
   const int* indx_in;
   int64_t ncol, pitch1, pitch2, y1_fstride, y2_fstride;
-  int km1, km2, nfields, CB, use_tma;
+  int km1, km2, nfields, CB, use_tma, P;
 };
 
-template <typename R, int MODE>
+template <typename R, int MODE, int LOG2P>
 __global__ void __launch_bounds__(256) k_lin_interp(const LiArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t bars[2];
@@ -134,29 +140,40 @@ __global__ void __launch_bounds__(256) k_lin_interp(const LiArgs a) {
     const R* sx1 = stage0 + (size_t)s * stage_elems;
     const R* sy1 = sx1 + n1p;
     const R* sx2 = sy1 + n1p * nf;
-    for (int u = warp; u < nc * chunks; u += nwarp) {
-      const int c = u / chunks, k2 = (u - c * chunks) * 32 + lane;
+    // work unit = (column, group of 32 consecutive targets); units are dealt round-robin to the warps
+    int c = warp / chunks, ch = warp - c * chunks;
+    while (c < nc) {
+      const int k2 = ch * 32 + lane;
       if (k2 < km2) {
         const R* x1c = sx1 + (size_t)c * a.pitch1;
         const R xt = sx2[(size_t)c * a.pitch2 + k2];
+        const size_t gcol = (size_t)(c0 + c);
         int k1;
-        if (MODE == LI_APPLY) k1 = a.indx_in[(size_t)(c0 + c) * km2 + k2];
-        else k1 = bracket<R>(x1c, km1, xt);
-        if (MODE != LI_APPLY && a.indx) a.indx[(size_t)(c0 + c) * km2 + k2] = k1;
+        if (MODE == LI_APPLY) k1 = a.indx_in[gcol * km2 + k2];
+        else k1 = bracket<R, LOG2P>(x1c, km1, a.P, xt);
+        if (MODE != LI_APPLY && a.indx) a.indx[gcol * km2 + k2] = k1;
         if (MODE != LI_SETUP) {
           const int k1ph = k1 == km1 - 1 ? k1 - 1 : k1 + 1;  // :119-131
           const R xa = x1c[k1], xb = x1c[k1ph];
           const R dxt = x_sub(xt, xa), dx = x_sub(xb, xa);
+          const R* y1c = sy1 + (size_t)c * a.pitch1;
+          R* gy = gy2 + gcol * a.pitch2 + k2;
           for (int f = 0; f < nf; ++f) {
-            const R* y1c = sy1 + n1p * f + (size_t)c * a.pitch1;
             const R ya = y1c[k1], yb = y1c[k1ph];
             R v = x_sub(yb, ya);  // :153
             v = x_mul(v, dxt);    // :154
             v = x_div(v, dx);     // :155
             v = x_add(v, ya);     // :156
-            st_stream(gy2 + (size_t)f * a.y2_fstride + (size_t)(c0 + c) * a.pitch2 + k2, v);
+            st_stream(gy, v);
+            y1c += n1p;
+            gy += a.y2_fstride;
           }
         }
+      }
+      ch += nwarp;
+      while (ch >= chunks) {
+        ch -= chunks;
+        ++c;
       }
     }
     __syncthreads();  // everyone is done with stage s before it is refilled two iterations from now
@@ -199,6 +216,9 @@ int lin_interp(int mode, const R* x1, const R* x2, const R* y1, R* y2, int* indx
   a.x1 = x1; a.x2 = x2; a.y1 = y1; a.y2 = y2; a.indx = indx; a.indx_in = indx_in;
   a.ncol = ncol; a.pitch1 = pitch1; a.pitch2 = pitch2; a.y1_fstride = y1_fstride; a.y2_fstride = y2_fstride;
   a.km1 = km1; a.km2 = km2; a.nfields = nfields; a.CB = CB; a.use_tma = use_tma ? 1 : 0;
+  int P = 1, log2p = 0;
+  while (2 * P <= km1) { P *= 2; ++log2p; }
+  a.P = P;
 
   const int64_t ntiles = (ncol + CB - 1) / CB;
   int per_sm = (int)(kMaxSmemPerCta / (smem + 1024));
@@ -210,22 +230,28 @@ int lin_interp(int mode, const R* x1, const R* x2, const R* y1, R* y2, int* indx
   if (getenv("EKAT_B200_DEBUG"))
     fprintf(stderr, "[ekat_b200] lin_interp mode=%d ncol=%lld km1=%d km2=%d p1=%lld p2=%lld nf=%d CB=%d smem=%zu grid=%u tma=%d\n",
             mode, (long long)ncol, km1, km2, (long long)pitch1, (long long)pitch2, nf, CB, smem, grid, (int)use_tma);
+#define EKB_LI_LAUNCH(MODE_, L2_)                      \
+  {                                                    \
+    auto k = k_lin_interp<R, MODE_, L2_>;              \
+    if ((rc = allow_smem(k, smem))) return rc;         \
+    k<<<grid, 256, smem, stream>>>(a);                 \
+  }
+#define EKB_LI_MODE(MODE_)                             \
+  if (log2p == 6) EKB_LI_LAUNCH(MODE_, 6)              \
+  else if (log2p == 7) EKB_LI_LAUNCH(MODE_, 7)         \
+  else EKB_LI_LAUNCH(MODE_, 0)
   if (mode == LI_FUSED) {
-    auto k = k_lin_interp<R, LI_FUSED>;
-    if ((rc = allow_smem(k, smem))) return rc;
-    k<<<grid, 256, smem, stream>>>(a);
+    EKB_LI_MODE(LI_FUSED)
     name = sizeof(R) == 8 ? "lin_interp<f64,fused>" : "lin_interp<f32,fused>";
   } else if (mode == LI_SETUP) {
-    auto k = k_lin_interp<R, LI_SETUP>;
-    if ((rc = allow_smem(k, smem))) return rc;
-    k<<<grid, 256, smem, stream>>>(a);
+    EKB_LI_MODE(LI_SETUP)
     name = sizeof(R) == 8 ? "lin_interp<f64,setup>" : "lin_interp<f32,setup>";
   } else {
-    auto k = k_lin_interp<R, LI_APPLY>;
-    if ((rc = allow_smem(k, smem))) return rc;
-    k<<<grid, 256, smem, stream>>>(a);
+    EKB_LI_LAUNCH(LI_APPLY, 0)
     name = sizeof(R) == 8 ? "lin_interp<f64,apply>" : "lin_interp<f32,apply>";
   }
+#undef EKB_LI_MODE
+#undef EKB_LI_LAUNCH
   note_launch(name);
   return check_cuda(cudaGetLastError());
 }

@@ -161,46 +161,47 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
     V* p0 = P0 + (size_t)k * LB * 32 + lane;
     V* p1 = P1 + (size_t)k * LB * 32 + lane;
     const V* p2 = P2 + (size_t)k * LB * 32 + lane;
+    // stage the whole chunk in registers first: one shared-memory latency per chunk instead of one per level
+    // (the in-place plane updates below would otherwise order every level's loads behind the previous stores)
+    V a[LB], b[LB], c[LB], x[LB], o0[LB], o1[LB];
 #pragma unroll
     for (int u = 0; u < LB; ++u) {
-      V a = ra[u * 32], x = p1[u * 32], b, c;
-      if (EXACT) {
-        b = p0[u * 32];
-        c = p2[u * 32];
-      } else {
-        b = rb[u * 32];
-        c = p0[u * 32];
-      }
-      if (u == 0 && k == 0) {  // dl(0) is never used (ekat_tridiag.hpp:24-27) and may hold anything
+      a[u] = ra[u * 32];
+      x[u] = p1[u * 32];
+      b[u] = EXACT ? p0[u * 32] : rb[u * 32];
+      c[u] = EXACT ? p2[u * 32] : p0[u * 32];
+    }
+    if (k == 0) {  // dl(0) is never used (ekat_tridiag.hpp:24-27) and may hold anything
 #pragma unroll
-        for (int j = 0; j < CPT; ++j) a.v[j] = (R)0;
-      }
-      V o0, o1;
+      for (int j = 0; j < CPT; ++j) a[0].v[j] = (R)0;
+    }
+#pragma unroll
+    for (int u = 0; u < LB; ++u) {
 #pragma unroll
       for (int j = 0; j < CPT; ++j) {
         if (EXACT) {
-          const R m = x_div_pipelined(a.v[j], q1[j]);        // dl(i) /= d(i-1)            :300
-          const R dc = x_sub(b.v[j], x_mul(m, cp[j]));       // d(i) -= dl(i)*du(i-1)      :301
-          const R xc = x_sub(x.v[j], x_mul(m, z1[j]));       // X(i) -= dl(i)*X(i-1)       :315-316
-          o0.v[j] = dc;
-          o1.v[j] = xc;
+          const R m = x_div_pipelined(a[u].v[j], q1[j]);      // dl(i) /= d(i-1)            :300
+          const R dc = x_sub(b[u].v[j], x_mul(m, cp[j]));     // d(i) -= dl(i)*du(i-1)      :301
+          const R xc = x_sub(x[u].v[j], x_mul(m, z1[j]));     // X(i) -= dl(i)*X(i-1)       :315-316
+          o0[u].v[j] = dc;
+          o1[u].v[j] = xc;
           q1[j] = dc;
           z1[j] = xc;
-          cp[j] = c.v[j];
+          cp[j] = c[u].v[j];
         } else {
           R q, z;
           if (u % RN == 0) {  // state was renormalised: q[i-1] == 1, q2 = q[i-2]/q[i-1]
-            q = f_fma(-(a.v[j] * cp[j]), q2[j], b.v[j]);
-            z = f_fma(-a.v[j], z1[j], x.v[j]);
+            q = f_fma(-(a[u].v[j] * cp[j]), q2[j], b[u].v[j]);
+            z = f_fma(-a[u].v[j], z1[j], x[u].v[j]);
           } else {
-            q = f_fma(b.v[j], q1[j], -((a.v[j] * cp[j]) * q2[j]));
-            z = f_fma(-a.v[j], z1[j], x.v[j] * q1[j]);
+            q = f_fma(b[u].v[j], q1[j], -((a[u].v[j] * cp[j]) * q2[j]));
+            z = f_fma(-a[u].v[j], z1[j], x[u].v[j] * q1[j]);
           }
           const R rq = t_rcp(q);
           const R g = (u % RN == 0) ? rq : q1[j] * rq;  // q[i-1]/q[i] = 1/pivot
           const R y = z * rq;
-          o0.v[j] = c.v[j] * g;
-          o1.v[j] = y;
+          o0[u].v[j] = c[u].v[j] * g;
+          o1[u].v[j] = y;
           if ((u + 1) % RN == 0) {  // renormalise: divide the state by q[i]
             q2[j] = g;
             z1[j] = y;
@@ -210,11 +211,14 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
             q1[j] = q;
             z1[j] = z;
           }
-          cp[j] = c.v[j];
+          cp[j] = c[u].v[j];
         }
       }
-      p0[u * 32] = o0;
-      p1[u * 32] = o1;
+    }
+#pragma unroll
+    for (int u = 0; u < LB; ++u) {
+      p0[u * 32] = o0[u];
+      p1[u * 32] = o1[u];
     }
     __syncwarp();  // every lane has read ring stage s
     if (lane == 0) {
@@ -267,8 +271,33 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
     }
   }
   for (int k = nfull - 1; k >= 0; --k) {
+    {
+      V* q1p = P1 + (size_t)k * LB * 32 + lane;
+      const V* q0p = P0 + (size_t)k * LB * 32 + lane;
+      const V* q2p = P2 + (size_t)k * LB * 32 + lane;
+      V y[LB], m0[LB], ui[LB];
 #pragma unroll
-    for (int u = LB - 1; u >= 0; --u) step((size_t)k * LB + u);
+      for (int u = 0; u < LB; ++u) {
+        y[u] = q1p[u * 32];
+        m0[u] = q0p[u * 32];
+        if (EXACT) ui[u] = q2p[u * 32];
+      }
+#pragma unroll
+      for (int u = LB - 1; u >= 0; --u) {
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+          if (EXACT) {
+            const R r = rcp_refined(m0[u].v[j]);  // off the x chain
+            xv[j] = div_given_rcp(x_sub(y[u].v[j], x_mul(ui[u].v[j], xv[j])), m0[u].v[j], r);  // :317-319
+          } else {
+            xv[j] = f_fma(-m0[u].v[j], xv[j], y[u].v[j]);
+          }
+          y[u].v[j] = xv[j];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < LB; ++u) q1p[u * 32] = y[u];
+    }
     fence_proxy_async();  // generic-proxy writes of this chunk -> visible to the TMA store
     __syncwarp();
     if (lane == 0) {
@@ -325,14 +354,13 @@ int tridiag_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, in
   const size_t bars = ((size_t)(8 + nch) * 8 + 127) & ~(size_t)127;
   const size_t planes = (size_t)(exact ? 3 : 2) * nch * chunk;
   const int nrings = exact ? 1 : 2;
-  // ring depth: 4 stages if that still leaves three CTAs per SM (or the column is short), else 2
-  int ns = 4;
-  const size_t third = (kMaxSmemPerCta + 1024) / 3 - 1024;  // per-CTA budget for 3 CTAs/SM (1 KB reserved per CTA)
-  if (bars + planes + (size_t)nrings * 4 * chunk > third && bars + planes + (size_t)nrings * 2 * chunk <= third) ns = 2;
+  // ring depth: 4 stages, or 2 if that lets one more CTA share the SM (measured: residency wins over ring depth)
+  auto per_sm = [&](int stages) { return (int)((kMaxSmemPerCta + 1024) / (bars + planes + (size_t)nrings * stages * chunk + 1024)); };
+  int ns = per_sm(2) > per_sm(4) ? 2 : 4;
   if (tu.cols_per_cta == 2 || tu.cols_per_cta == 4) ns = tu.cols_per_cta;  // tuning override: ring stages
   const size_t smem = bars + planes + (size_t)nrings * ns * chunk;
   if (smem > kMaxSmemPerCta) return EKAT_B200_ERR_UNSUPPORTED;
-  int pd = tu.prefetch > 0 ? tu.prefetch : 6;  // plane chunks in flight ahead of the sweep
+  int pd = tu.prefetch > 0 ? tu.prefetch : 3;  // plane chunks in flight ahead of the sweep
   if (pd < 1) pd = 1;
   const bool f64 = sizeof(R) == 8;
   const char* name = exact ? (f64 ? "tridiag_tma<f64,bfb>" : "tridiag_tma<f32,bfb>")
