@@ -33,18 +33,35 @@ enum LiMode { LI_FUSED = 0, LI_SETUP = 1, LI_APPLY = 2 };
 // "if (idx > 0) --idx" (:179-181). Branch-free: one probe picks the power-of-two window [0,P) or [km1-P,km1)
 // (P = bit_floor(km1)) that must contain the boundary, then log2(P) probes with halving steps and a last one --
 // each a shared-memory load, a compare and a predicated add. LOG2P > 0: unrolled for that window; 0: loop.
+__device__ __forceinline__ double lds_at(unsigned addr, double) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float lds_at(unsigned addr, float) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+// The running position is a 32-bit shared-memory byte address, so that a probe is exactly: load [p + const],
+// compare, predicated add (generic 64-bit pointers cost the compiler five extra instructions per probe).
 template <typename R, int LOG2P>
-__device__ __forceinline__ int bracket(const R* __restrict__ x1, int km1, int P, R v) {
-  int pos = (km1 > P && v >= x1[km1 - P - 1]) ? km1 - P : 0;
+__device__ __forceinline__ int bracket(unsigned x1, int km1, int P, R v) {
+  constexpr unsigned B = sizeof(R);
+  unsigned p = x1;
+  if (km1 > P) {
+    if (v >= lds_at(x1 + (unsigned)(km1 - P - 1) * B, R())) p += (unsigned)(km1 - P) * B;
+  }
   if (LOG2P > 0) {
 #pragma unroll
     for (int b = LOG2P - 1; b >= 0; --b)
-      if (v >= x1[pos + (1 << b) - 1]) pos += 1 << b;
+      if (v >= lds_at(p + ((1u << b) - 1u) * B, R())) p += B << b;
   } else {
     for (int step = P >> 1; step >= 1; step >>= 1)
-      if (v >= x1[pos + step - 1]) pos += step;
+      if (v >= lds_at(p + (unsigned)(step - 1) * B, R())) p += (unsigned)step * B;
   }
-  if (v >= x1[pos]) pos += 1;
+  if (v >= lds_at(p, R())) p += B;
+  const int pos = (int)((p - x1) / B);
   return pos > 0 ? pos - 1 : pos;
 }
 
@@ -77,7 +94,6 @@ __global__ void __launch_bounds__(256) k_lin_interp(const LiArgs a) {
 
   const int64_t ntiles = (a.ncol + CB - 1) / CB;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
-  const int chunks = (km2 + 31) / 32;
 
   if (tid == 0) {
     mbar_init(&bars[0], 1);
@@ -140,24 +156,30 @@ __global__ void __launch_bounds__(256) k_lin_interp(const LiArgs a) {
     const R* sx1 = stage0 + (size_t)s * stage_elems;
     const R* sy1 = sx1 + n1p;
     const R* sx2 = sy1 + n1p * nf;
-    // work unit = (column, group of 32 consecutive targets); units are dealt round-robin to the warps
-    int c = warp / chunks, ch = warp - c * chunks;
-    while (c < nc) {
-      const int k2 = ch * 32 + lane;
-      if (k2 < km2) {
-        const R* x1c = sx1 + (size_t)c * a.pitch1;
-        const R xt = sx2[(size_t)c * a.pitch2 + k2];
-        const size_t gcol = (size_t)(c0 + c);
+    // one warp per column (CB is a multiple of the warp count whenever a stage can hold that many columns):
+    // per-column addresses are formed once, lanes walk the targets 32 at a time
+    const int p1 = (int)a.pitch1, p2 = (int)a.pitch2, P = a.P;
+    for (int c = warp; c < nc; c += nwarp) {
+      const R* x1c = sx1 + c * p1;
+      const R* x2c = sx2 + c * p2;
+      const unsigned x1a = smem_u32(x1c);
+      const R* y1c0 = sy1 + c * p1;
+      const size_t gcol = (size_t)(c0 + c);
+      R* gyc = gy2 + gcol * p2;
+      int* gic = (MODE != LI_APPLY && a.indx) ? a.indx + gcol * km2 : nullptr;
+      const int* gin = MODE == LI_APPLY ? a.indx_in + gcol * km2 : nullptr;
+      for (int k2 = lane; k2 < km2; k2 += 32) {
+        const R xt = x2c[k2];
         int k1;
-        if (MODE == LI_APPLY) k1 = a.indx_in[gcol * km2 + k2];
-        else k1 = bracket<R, LOG2P>(x1c, km1, a.P, xt);
-        if (MODE != LI_APPLY && a.indx) a.indx[gcol * km2 + k2] = k1;
+        if (MODE == LI_APPLY) k1 = gin[k2];
+        else k1 = bracket<R, LOG2P>(x1a, km1, P, xt);
+        if (gic) gic[k2] = k1;
         if (MODE != LI_SETUP) {
           const int k1ph = k1 == km1 - 1 ? k1 - 1 : k1 + 1;  // :119-131
           const R xa = x1c[k1], xb = x1c[k1ph];
           const R dxt = x_sub(xt, xa), dx = x_sub(xb, xa);
-          const R* y1c = sy1 + (size_t)c * a.pitch1;
-          R* gy = gy2 + gcol * a.pitch2 + k2;
+          const R* y1c = y1c0;
+          R* gy = gyc + k2;
           for (int f = 0; f < nf; ++f) {
             const R ya = y1c[k1], yb = y1c[k1ph];
             R v = x_sub(yb, ya);  // :153
@@ -169,11 +191,6 @@ __global__ void __launch_bounds__(256) k_lin_interp(const LiArgs a) {
             gy += a.y2_fstride;
           }
         }
-      }
-      ch += nwarp;
-      while (ch >= chunks) {
-        ch -= chunks;
-        ++c;
       }
     }
     __syncthreads();  // everyone is done with stage s before it is refilled two iterations from now
@@ -196,6 +213,7 @@ int lin_interp(int mode, const R* x1, const R* x2, const R* y1, R* y2, int* indx
   const Tuning tu = tuning();
   int CB = tu.cols_per_cta > 0 ? tu.cols_per_cta : (int)((24 * 1024) / col_bytes);
   if (CB > 64) CB = 64;
+  if (tu.cols_per_cta <= 0) CB = CB >= 8 ? (CB & ~7) : 8;  // a multiple of the 8 warps: one column per warp per round
   if (CB > 1) CB &= ~1;  // even -> tile byte counts are multiples of 16 for f64
   if (sizeof(R) == 4 && CB > 3) CB &= ~3;
   if (CB < 1) CB = 1;
