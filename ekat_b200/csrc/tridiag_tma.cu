@@ -79,6 +79,53 @@ __device__ __forceinline__ float t_rcp(float x) {
 
 constexpr int kLB = 8;  // levels per TMA box / mbarrier phase / unrolled chunk
 
+// bfb sweeps over one chunk of LB levels held in registers. SLOW = false: speculative IEEE division (div_spec: no
+// branch on the dependent chain, out-of-range operands only raise `bad`); SLOW = true: the compiler's full-range
+// division. The kernel runs the speculative form and repeats the chunk in SLOW form if any lane raised the flag.
+template <typename R, int CPT, int LB, bool SLOW>
+__device__ __forceinline__ void bfb_fwd_chunk(const Vec<R, CPT> (&a)[LB], const Vec<R, CPT> (&b)[LB], const Vec<R, CPT> (&c)[LB],
+                                              const Vec<R, CPT> (&x)[LB], Vec<R, CPT> (&o0)[LB], Vec<R, CPT> (&o1)[LB],
+                                              R (&dprev)[CPT], R (&xprev)[CPT], R (&uprev)[CPT], bool first, bool& bad) {
+#pragma unroll
+  for (int u = 0; u < LB; ++u) {
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      R m;
+      if (SLOW) {
+        m = x_div(a[u].v[j], dprev[j]);
+      } else {
+        bool f = false;
+        m = div_spec(a[u].v[j], dprev[j], rcp_refined(dprev[j]), f);
+        if (u == 0) f = f && !first;  // level 0 of a column has no multiplier
+        bad = bad || f;
+      }
+      if (u == 0) m = first ? (R)0 : m;                   // dl(0) is never used (ekat_tridiag.hpp:24-27)
+      const R dc = x_sub(b[u].v[j], x_mul(m, uprev[j]));  // d(i) -= dl(i)*du(i-1)      :301
+      const R xc = x_sub(x[u].v[j], x_mul(m, xprev[j]));  // X(i) -= dl(i)*X(i-1)       :315-316
+      o0[u].v[j] = dc;
+      o1[u].v[j] = xc;
+      dprev[j] = dc;
+      xprev[j] = xc;
+      uprev[j] = c[u].v[j];
+    }
+  }
+}
+template <typename R, int CPT, int LB, bool SLOW>
+__device__ __forceinline__ void bfb_bwd_chunk(Vec<R, CPT> (&y)[LB], const Vec<R, CPT> (&dd)[LB], const Vec<R, CPT> (&ui)[LB],
+                                              R (&xv)[CPT], bool& bad) {
+#pragma unroll
+  for (int u = LB - 1; u >= 0; --u) {
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      const R num = x_sub(y[u].v[j], x_mul(ui[u].v[j], xv[j]));  // X(i-1) - du(i-1)*X(i)   :318-319
+      if (SLOW) xv[j] = x_div(num, dd[u].v[j]);
+      else xv[j] = div_spec(num, dd[u].v[j], rcp_refined(dd[u].v[j]), bad);  // reciprocal is off the x chain
+      y[u].v[j] = xv[j];
+    }
+  }
+}
+
+
 // ------------------------------------------------------------------------------------------- the kernel
 // grid = (column tiles, matrices); block = 32 threads. Lane l owns columns c0 + l*CPT .. +CPT-1.
 // Shared memory: [ring barriers NS][plane barriers nch] | planes [level][lane] | rings [stage][LB][lane].
@@ -97,15 +144,16 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
   const int lane = threadIdx.x;
   const int nfull = nlev / LB, ntail = nlev - nfull * LB, nch = nfull + (ntail ? 1 : 0);
 
+  // barriers: ring[NS] | plane[nch] | backward du ring[2*NS] (EXACT)
   uint64_t* rbar = reinterpret_cast<uint64_t*>(smem_raw);
   uint64_t* pbar = rbar + NS;
-  const size_t off = ((size_t)(NS + nch) * 8 + 127) & ~(size_t)127;
+  uint64_t* bbar = pbar + nch;
+  const size_t off = ((size_t)(3 * NS + nch) * 8 + 127) & ~(size_t)127;
   const size_t plane = (size_t)nch * LB * 32;  // V units
   V* P0 = reinterpret_cast<V*>(smem_raw + off);
   V* P1 = P0 + plane;
-  V* P2 = P1 + plane;                       // EXACT only
-  V* RA = EXACT ? P2 + plane : P1 + plane;  // dl ring
-  V* RB = RA + (size_t)NS * LB * 32;        // d ring (FAST only)
+  V* RA = P1 + plane;                 // dl ring [NS][LB][32]
+  V* RB = RA + (size_t)NS * LB * 32;  // FAST: d ring; EXACT: du ring. EXACT back-substitution: RA..RB = one du ring of 2*NS stages
 
   const int c0 = blockIdx.x * W;
   const int row0 = blockIdx.y * nlev;
@@ -113,26 +161,34 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
   if (lane == 0) {
     for (int s = 0; s < NS; ++s) mbar_init(&rbar[s], 1);
     for (int k = 0; k < nch; ++k) mbar_init(&pbar[k], 1);
+    if (EXACT)
+      for (int s = 0; s < 2 * NS; ++s) mbar_init(&bbar[s], 1);
     fence_mbar_init();
   }
   __syncwarp();
 
+  // L2 policies: every operand is read once (evict-first) except bfb's du, which the back-substitution reads
+  // again ~20 us later: it is kept in the 126 MB L2 (evict-last) instead of in a third shared-memory plane,
+  // which is what lets three bfb CTAs share an SM.
+  const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
+
   auto issue_ring = [&](int k) {
     const int s = k % NS;
-    mbar_expect_tx(&rbar[s], (EXACT ? 1u : 2u) * CHUNK_BYTES);
-    tma_load_2d(RA + (size_t)s * LB * 32, &mdl, c0, row0 + k * LB, &rbar[s]);
-    if (!EXACT) tma_load_2d(RB + (size_t)s * LB * 32, &md, c0, row0 + k * LB, &rbar[s]);
+    mbar_expect_tx(&rbar[s], 2u * CHUNK_BYTES);
+    tma_load_2d_hint(RA + (size_t)s * LB * 32, &mdl, c0, row0 + k * LB, &rbar[s], pol_stream);
+    if (EXACT) tma_load_2d_hint(RB + (size_t)s * LB * 32, &mdu, c0, row0 + k * LB, &rbar[s], pol_keep);
+    else tma_load_2d_hint(RB + (size_t)s * LB * 32, &md, c0, row0 + k * LB, &rbar[s], pol_stream);
   };
   auto issue_plane = [&](int k) {
     const size_t o = (size_t)k * LB * 32;
-    mbar_expect_tx(&pbar[k], (EXACT ? 3u : 2u) * CHUNK_BYTES);
-    if (EXACT) {
-      tma_load_2d(P0 + o, &md, c0, row0 + k * LB, &pbar[k]);
-      tma_load_2d(P2 + o, &mdu, c0, row0 + k * LB, &pbar[k]);
-    } else {
-      tma_load_2d(P0 + o, &mdu, c0, row0 + k * LB, &pbar[k]);
-    }
-    tma_load_2d(P1 + o, &mx, c0, row0 + k * LB, &pbar[k]);
+    mbar_expect_tx(&pbar[k], 2u * CHUNK_BYTES);
+    tma_load_2d_hint(P0 + o, EXACT ? &md : &mdu, c0, row0 + k * LB, &pbar[k], pol_stream);
+    tma_load_2d_hint(P1 + o, &mx, c0, row0 + k * LB, &pbar[k], pol_stream);
+  };
+  auto issue_back = [&](int j) {  // EXACT: du of chunk nch-1-j for the back-substitution
+    const int s = j % (2 * NS);
+    mbar_expect_tx(&bbar[s], CHUNK_BYTES);
+    tma_load_2d_hint(RA + (size_t)s * LB * 32, &mdu, c0, row0 + (nch - 1 - j) * LB, &bbar[s], pol_stream);
   };
   if (lane == 0) {
     const int n0 = pd > NS ? pd : NS;
@@ -160,7 +216,6 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
     const V* rb = RB + (size_t)s * LB * 32 + lane;
     V* p0 = P0 + (size_t)k * LB * 32 + lane;
     V* p1 = P1 + (size_t)k * LB * 32 + lane;
-    const V* p2 = P2 + (size_t)k * LB * 32 + lane;
     // stage the whole chunk in registers first: one shared-memory latency per chunk instead of one per level
     // (the in-place plane updates below would otherwise order every level's loads behind the previous stores)
     V a[LB], b[LB], c[LB], x[LB], o0[LB], o1[LB];
@@ -169,26 +224,36 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
       a[u] = ra[u * 32];
       x[u] = p1[u * 32];
       b[u] = EXACT ? p0[u * 32] : rb[u * 32];
-      c[u] = EXACT ? p2[u * 32] : p0[u * 32];
+      c[u] = EXACT ? rb[u * 32] : p0[u * 32];
     }
-    if (k == 0) {  // dl(0) is never used (ekat_tridiag.hpp:24-27) and may hold anything
-#pragma unroll
-      for (int j = 0; j < CPT; ++j) a[0].v[j] = (R)0;
-    }
-#pragma unroll
-    for (int u = 0; u < LB; ++u) {
+    if (EXACT) {
+      R sd[CPT], sx[CPT], su[CPT];
 #pragma unroll
       for (int j = 0; j < CPT; ++j) {
-        if (EXACT) {
-          const R m = x_div_pipelined(a[u].v[j], q1[j]);      // dl(i) /= d(i-1)            :300
-          const R dc = x_sub(b[u].v[j], x_mul(m, cp[j]));     // d(i) -= dl(i)*du(i-1)      :301
-          const R xc = x_sub(x[u].v[j], x_mul(m, z1[j]));     // X(i) -= dl(i)*X(i-1)       :315-316
-          o0[u].v[j] = dc;
-          o1[u].v[j] = xc;
-          q1[j] = dc;
-          z1[j] = xc;
-          cp[j] = c[u].v[j];
-        } else {
+        sd[j] = q1[j];
+        sx[j] = z1[j];
+        su[j] = cp[j];
+      }
+      bool bad = false;
+      bfb_fwd_chunk<R, CPT, LB, false>(a, b, c, x, o0, o1, q1, z1, cp, k == 0, bad);
+      if (__any_sync(0xffffffffu, bad)) {  // rare operands somewhere in the warp: redo with the full-range division
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+          q1[j] = sd[j];
+          z1[j] = sx[j];
+          cp[j] = su[j];
+        }
+        bfb_fwd_chunk<R, CPT, LB, true>(a, b, c, x, o0, o1, q1, z1, cp, k == 0, bad);
+      }
+    } else {
+      if (k == 0) {  // dl(0) is never used (ekat_tridiag.hpp:24-27) and may hold anything
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) a[0].v[j] = (R)0;
+      }
+#pragma unroll
+      for (int u = 0; u < LB; ++u) {
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) {
           R q, z;
           if (u % RN == 0) {  // state was renormalised: q[i-1] == 1, q2 = q[i-2]/q[i-1]
             q = f_fma(-(a[u].v[j] * cp[j]), q2[j], b[u].v[j]);
@@ -226,83 +291,104 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
       if (k + pd < nch) issue_plane(k + pd);
     }
   }
-  // du(nrow-1) is never used (:24-27): zero the coupling of the last level so the back-substitution is uniform
-  {
+  // du(nrow-1) is never used (:24-27): the coupling of the last level is zeroed so the back-substitution is uniform
+  if (!EXACT) {
     V zero;
 #pragma unroll
     for (int j = 0; j < CPT; ++j) zero.v[j] = (R)0;
-    (EXACT ? P2 : P0)[(size_t)(nlev - 1) * 32 + lane] = zero;
+    P0[(size_t)(nlev - 1) * 32 + lane] = zero;
+  } else if (lane == 0) {
+    for (int j = 0; j < 2 * NS && j < nch; ++j) issue_back(j);  // both rings are free now: refill them with du from L2
   }
 
   // ---------------------------------------------------------------- back substitution
   R xv[CPT];
 #pragma unroll
   for (int j = 0; j < CPT; ++j) xv[j] = (R)0;
-  auto step = [&](size_t i) {
-    const size_t e = i * 32 + lane;
-    const V y = P1[e], m0 = P0[e];
-    V o;
-    if (EXACT) {
-      const V ui = P2[e];
+  for (int jb = 0; jb < nch; ++jb) {
+    const int k = nch - 1 - jb;
+    V* q1p = P1 + (size_t)k * LB * 32 + lane;
+    const V* q0p = P0 + (size_t)k * LB * 32 + lane;
+    const V* bu = RA + (size_t)(jb % (2 * NS)) * LB * 32 + lane;
+    if (EXACT) mbar_wait(&bbar[jb % (2 * NS)], (unsigned)(jb / (2 * NS)) & 1u);
+    if (k == nfull) {
+      // partial top chunk: a tensor store would spill into the next matrix' rows -> plain streaming stores
+      const int64_t col = (int64_t)c0 + lane * CPT;
+      for (int u = ntail - 1; u >= 0; --u) {
+        const V y = q1p[u * 32], m0 = q0p[u * 32];
+        V o;
+        if (EXACT) {
+          V ui = bu[u * 32];
+          if (u == ntail - 1) {
 #pragma unroll
-      for (int j = 0; j < CPT; ++j) {
-        const R r = rcp_refined(m0.v[j]);  // off the x chain
-        xv[j] = div_given_rcp(x_sub(y.v[j], x_mul(ui.v[j], xv[j])), m0.v[j], r);  // :317-319
-        o.v[j] = xv[j];
+            for (int j = 0; j < CPT; ++j) ui.v[j] = (R)0;
+          }
+#pragma unroll
+          for (int j = 0; j < CPT; ++j) {
+            xv[j] = x_div(x_sub(y.v[j], x_mul(ui.v[j], xv[j])), m0.v[j]);  // :317-319
+            o.v[j] = xv[j];
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < CPT; ++j) {
+            xv[j] = f_fma(-m0.v[j], xv[j], y.v[j]);
+            o.v[j] = xv[j];
+          }
+        }
+        R* g = X + (size_t)(row0 + k * LB + u) * x_stride + col;
+#pragma unroll
+        for (int j = 0; j < CPT; ++j)
+          if (col + j < ncol) __stcs(g + j, o.v[j]);
       }
     } else {
-#pragma unroll
-      for (int j = 0; j < CPT; ++j) {
-        xv[j] = f_fma(-m0.v[j], xv[j], y.v[j]);
-        o.v[j] = xv[j];
-      }
-    }
-    P1[e] = o;
-    return o;
-  };
-  if (ntail) {  // partial chunk: a tensor store would spill into the next matrix' rows -> plain stores
-    const int64_t col = (int64_t)c0 + lane * CPT;
-    for (int i = nlev - 1; i >= nfull * LB; --i) {
-      const V o = step((size_t)i);
-      R* g = X + (size_t)(row0 + i) * x_stride + col;
-#pragma unroll
-      for (int j = 0; j < CPT; ++j)
-        if (col + j < ncol) __stcs(g + j, o.v[j]);
-    }
-  }
-  for (int k = nfull - 1; k >= 0; --k) {
-    {
-      V* q1p = P1 + (size_t)k * LB * 32 + lane;
-      const V* q0p = P0 + (size_t)k * LB * 32 + lane;
-      const V* q2p = P2 + (size_t)k * LB * 32 + lane;
       V y[LB], m0[LB], ui[LB];
 #pragma unroll
       for (int u = 0; u < LB; ++u) {
         y[u] = q1p[u * 32];
         m0[u] = q0p[u * 32];
-        if (EXACT) ui[u] = q2p[u * 32];
+        if (EXACT) ui[u] = bu[u * 32];
       }
+      if (EXACT) {
+        if (jb == 0) {  // this chunk ends with the last level
 #pragma unroll
-      for (int u = LB - 1; u >= 0; --u) {
+          for (int j = 0; j < CPT; ++j) ui[LB - 1].v[j] = (R)0;
+        }
+        R sxv[CPT];
+        V ys[LB];
 #pragma unroll
-        for (int j = 0; j < CPT; ++j) {
-          if (EXACT) {
-            const R r = rcp_refined(m0[u].v[j]);  // off the x chain
-            xv[j] = div_given_rcp(x_sub(y[u].v[j], x_mul(ui[u].v[j], xv[j])), m0[u].v[j], r);  // :317-319
-          } else {
+        for (int j = 0; j < CPT; ++j) sxv[j] = xv[j];
+#pragma unroll
+        for (int u = 0; u < LB; ++u) ys[u] = y[u];
+        bool bad = false;
+        bfb_bwd_chunk<R, CPT, LB, false>(y, m0, ui, xv, bad);
+        if (__any_sync(0xffffffffu, bad)) {
+#pragma unroll
+          for (int j = 0; j < CPT; ++j) xv[j] = sxv[j];
+#pragma unroll
+          for (int u = 0; u < LB; ++u) y[u] = ys[u];
+          bfb_bwd_chunk<R, CPT, LB, true>(y, m0, ui, xv, bad);
+        }
+      } else {
+#pragma unroll
+        for (int u = LB - 1; u >= 0; --u) {
+#pragma unroll
+          for (int j = 0; j < CPT; ++j) {
             xv[j] = f_fma(-m0[u].v[j], xv[j], y[u].v[j]);
+            y[u].v[j] = xv[j];
           }
-          y[u].v[j] = xv[j];
         }
       }
 #pragma unroll
       for (int u = 0; u < LB; ++u) q1p[u * 32] = y[u];
+      fence_proxy_async();  // generic-proxy writes of this chunk -> visible to the TMA store
     }
-    fence_proxy_async();  // generic-proxy writes of this chunk -> visible to the TMA store
-    __syncwarp();
+    __syncwarp();  // every lane has read its du stage / written its part of the chunk
     if (lane == 0) {
-      tma_store_2d(&mx, c0, row0 + k * LB, P1 + (size_t)k * LB * 32);
-      tma_store_commit();
+      if (k != nfull) {
+        tma_store_2d(&mx, c0, row0 + k * LB, P1 + (size_t)k * LB * 32);
+        tma_store_commit();
+      }
+      if (EXACT && jb + 2 * NS < nch) issue_back(jb + 2 * NS);
     }
   }
   if (lane == 0) tma_store_wait_read<0>();  // shared memory must outlive the stores' reads
@@ -351,9 +437,9 @@ int tridiag_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, in
   const Tuning tu = tuning();
   const int nch = (nlev + kLB - 1) / kLB;
   const size_t chunk = (size_t)kLB * W * sizeof(R);
-  const size_t bars = ((size_t)(8 + nch) * 8 + 127) & ~(size_t)127;
-  const size_t planes = (size_t)(exact ? 3 : 2) * nch * chunk;
-  const int nrings = exact ? 1 : 2;
+  const size_t bars = ((size_t)(12 + nch) * 8 + 127) & ~(size_t)127;
+  const size_t planes = (size_t)2 * nch * chunk;
+  const int nrings = 2;
   // ring depth: 4 stages, or 2 if that lets one more CTA share the SM (measured: residency wins over ring depth)
   auto per_sm = [&](int stages) { return (int)((kMaxSmemPerCta + 1024) / (bars + planes + (size_t)nrings * stages * chunk + 1024)); };
   int ns = per_sm(2) > per_sm(4) ? 2 : 4;

@@ -225,6 +225,14 @@ __global__ void k_selftest_div(uint64_t n, uint64_t seed, int mode, unsigned lon
     }
     const R q = x_div_pipelined(a, b), w = DivRef<R>::ref(a, b);
     if (DivRef<R>::bits(q) != DivRef<R>::bits(w) && !(q != q && w != w)) ++bad;
+    // the speculative form must be right whenever it does not raise its flag; also probe zero numerators
+    for (int z = 0; z < 2; ++z) {
+      const R an = z ? (R)0 : a;
+      bool flagged = false;
+      const R qs = div_spec(an, b, rcp_refined(b), flagged);
+      const R ws = DivRef<R>::ref(an, b);
+      if (!flagged && DivRef<R>::bits(qs) != DivRef<R>::bits(ws) && !(qs != qs && ws != ws)) ++bad;
+    }
   }
   if (bad) atomicAdd(mismatches, bad);
 }
