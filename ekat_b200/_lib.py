@@ -42,6 +42,7 @@ _SIGS["ekat_b200_last_cuda_error"] = []
 _SIGS["ekat_b200_launch_count"] = []
 _SIGS["ekat_b200_last_kernel"] = []
 _SIGS["ekat_b200_set_tuning"] = [cint, cint, cint]
+_SIGS["ekat_b200_debug_trace"] = [vp, cint]
 
 STATUS = {0: "OK", -1: "ERR_INVALID", -2: "ERR_UNSUPPORTED", -3: "ERR_CUDA", -4: "ERR_TOO_LARGE"}
 

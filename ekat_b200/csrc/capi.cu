@@ -38,6 +38,8 @@ template <typename R>
 int residual(const R* dl, const R* d, const R* du, const R* B, const R* X, int64_t ncol, int nlev, int nA, int nrhs,
              int64_t pitch, double* out, cudaStream_t st);
 
+int debug_trace(long long* out, int n);
+
 template <typename R>
 int selftest_div(uint64_t n, uint64_t seed, int mode, uint64_t* mismatches, cudaStream_t st);
 
@@ -222,6 +224,10 @@ int ekat_b200_device_alloc(void** ptr, size_t bytes) {
   return check_cuda(cudaMalloc(ptr, bytes));
 }
 int ekat_b200_device_free(void* ptr) { return ptr ? check_cuda(cudaFree(ptr)) : EKAT_B200_OK; }
+
+int ekat_b200_debug_trace(int64_t* out, int n) {
+  return (out && n > 0) ? debug_trace(reinterpret_cast<long long*>(out), n) : EKAT_B200_ERR_INVALID;
+}
 
 int ekat_b200_version(void) { return EKAT_B200_VERSION; }
 const char* ekat_b200_last_cuda_error(void) { return ekb::t_err; }

@@ -35,6 +35,11 @@ template <typename R>
 int tridiag_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride,
                 int64_t x_stride, cudaStream_t stream);
 
+// Persistent TMA-fed kernel for one matrix shared by nrhs right-hand sides (tridiag_tma_shared.cu).
+template <typename R>
+int tridiag_tma_shared(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nrhs, int64_t a_stride,
+                       int64_t x_stride, cudaStream_t stream);
+
 // ---------------------------------------------------------------------------------------
 // One matrix per rhs (nA == nrhs, incl. nrhs == 1): thread <-> (column group, blockIdx.y = matrix).
 // Planes ([nlev][T] vectors):  EXACT: P0 = d -> d', P1 = x -> x', P2 = du;  ring R0 = dl
@@ -322,6 +327,10 @@ int tridiag_levmajor(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nle
   const bool clobber = (flags & EKAT_B200_CLOBBER_DIAGS) != 0;
   if (nA == nrhs && !clobber && tuning().variant == 0) {
     const int rc = tridiag_tma<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
+    if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+  }
+  if (nA == 1 && nrhs > 1 && !clobber && (tuning().variant == 0 || tuning().variant == 7)) {
+    const int rc = tridiag_tma_shared<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }
   constexpr int VEC = 16 / sizeof(R);

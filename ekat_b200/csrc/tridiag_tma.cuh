@@ -1,0 +1,91 @@
+// tridiag_tma.cuh -- pieces shared by the TMA-fed level-major tridiagonal kernels
+// (tridiag_tma.cu: one matrix per right-hand side; tridiag_tma_shared.cu: one matrix, many right-hand sides).
+#pragma once
+#include <cuda.h>
+
+#include "tridiag_lm_common.cuh"
+
+namespace ekb {
+
+// [nrows][pitch] array of R, of which the first ncol entries of a row are data; box = boxc columns x boxr rows.
+// Columns beyond ncol / rows beyond nrows read as zero and are not written (TMA bounds handling). tridiag_tma.cu.
+template <typename R>
+bool make_tensor_map_2d(CUtensorMap* m, const R* base, int64_t ncol, int64_t nrows, int64_t pitch, int boxc, int boxr);
+
+// Reciprocal for the ratio form: hardware seed (~2^-20) and one cubic Newton step (~2^-60 relative; eps is 2^-53).
+__device__ __forceinline__ double t_rcp(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double e = fma(-x, r, 1.0);
+  e = fma(e, e, e);
+  return fma(r, e, r);
+}
+__device__ __forceinline__ float t_rcp(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  const float e = fmaf(-x, r, 1.0f);
+  return fmaf(r, e, r);
+}
+
+// columns per lane and renormalisation interval of the ratio-form recurrence, per precision
+template <typename R>
+struct TmaCfg;
+template <>
+struct TmaCfg<double> {
+  static constexpr int CPT = 1, RN = 8;
+};
+template <>
+struct TmaCfg<float> {
+  static constexpr int CPT = 2, RN = 2;
+};
+
+constexpr int kLB = 8;  // levels per TMA box / mbarrier phase / unrolled chunk
+
+// bfb sweeps over one chunk of LB levels held in registers. SLOW = false: speculative IEEE division (div_spec: no
+// branch on the dependent chain, out-of-range operands only raise `bad`); SLOW = true: the compiler's full-range
+// division. The kernel runs the speculative form and repeats the chunk in SLOW form if any lane raised the flag.
+template <typename R, int CPT, int LB, bool SLOW>
+__device__ __forceinline__ void bfb_fwd_chunk(const Vec<R, CPT> (&a)[LB], const Vec<R, CPT> (&b)[LB], const Vec<R, CPT> (&c)[LB],
+                                              const Vec<R, CPT> (&x)[LB], Vec<R, CPT> (&o0)[LB], Vec<R, CPT> (&o1)[LB],
+                                              R (&dprev)[CPT], R (&xprev)[CPT], R (&uprev)[CPT], bool first, bool& bad) {
+#pragma unroll
+  for (int u = 0; u < LB; ++u) {
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      R m;
+      if (SLOW) {
+        m = x_div(a[u].v[j], dprev[j]);
+      } else {
+        bool f = false;
+        m = div_spec(a[u].v[j], dprev[j], rcp_refined(dprev[j]), f);
+        if (u == 0) f = f && !first;  // level 0 of a column has no multiplier
+        bad = bad || f;
+      }
+      if (u == 0) m = first ? (R)0 : m;                   // dl(0) is never used (ekat_tridiag.hpp:24-27)
+      const R dc = x_sub(b[u].v[j], x_mul(m, uprev[j]));  // d(i) -= dl(i)*du(i-1)      :301
+      const R xc = x_sub(x[u].v[j], x_mul(m, xprev[j]));  // X(i) -= dl(i)*X(i-1)       :315-316
+      o0[u].v[j] = dc;
+      o1[u].v[j] = xc;
+      dprev[j] = dc;
+      xprev[j] = xc;
+      uprev[j] = c[u].v[j];
+    }
+  }
+}
+template <typename R, int CPT, int LB, bool SLOW>
+__device__ __forceinline__ void bfb_bwd_chunk(Vec<R, CPT> (&y)[LB], const Vec<R, CPT> (&dd)[LB], const Vec<R, CPT> (&ui)[LB],
+                                              R (&xv)[CPT], bool& bad) {
+#pragma unroll
+  for (int u = LB - 1; u >= 0; --u) {
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      const R num = x_sub(y[u].v[j], x_mul(ui[u].v[j], xv[j]));  // X(i-1) - du(i-1)*X(i)   :318-319
+      if (SLOW) xv[j] = x_div(num, dd[u].v[j]);
+      else xv[j] = div_spec(num, dd[u].v[j], rcp_refined(dd[u].v[j]), bad);  // reciprocal is off the x chain
+      y[u].v[j] = xv[j];
+    }
+  }
+}
+
+
+}  // namespace ekb

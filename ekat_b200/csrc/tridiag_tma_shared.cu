@@ -1,0 +1,544 @@
+// tridiag_tma_shared.cu -- batched Thomas / bfb, ONE matrix shared by many right-hand sides (nA == 1, nrhs > 1),
+// native level-major layout, TMA-fed, persistent warp-specialised CTAs.
+//
+// Replaces the per-column loops around ekat::tridiag::thomas(team, dl, d, du, X[nrow][nrhs])
+// (reference src/algorithm/ekat_tridiag.hpp:177-214, :323-334: factorize once in Kokkos::single, barrier, one
+// solve per right-hand side) and ekat::tridiag::bfb with rank-1 A (:292-320, :632-648) -- BASELINE config 4
+// (10 tracers diffused by one SHOC-style matrix per column).
+//
+// Why this shape. Per column-level the kernel moves 3 + 2*nrhs words and does ~5*nrhs flops, so it is HBM-bound
+// as long as the forward sweep's intermediates never leave the chip: a tile of 32 columns x 128 levels needs one
+// plane (32 KB, f64) per right-hand side plus one for the factor, i.e. five right-hand sides fill an SM. With one
+// CTA per SM nothing hides a tile's load latency unless the CTA itself overlaps tiles, hence:
+//  * persistent CTAs walk work items (column tile, group of rh right-hand sides);
+//  * warp roles: rh solver warps (one right-hand side each, lane = column), one factor warp, two producer warps
+//    (one elected lane each) that only issue TMA copies -- every wait in the kernel is an mbarrier wait;
+//  * the factor warp turns (dl, d) into (m, r) [thomas] or (dl) into (m) [bfb] in place in a ring stage that the
+//    TMA filled and hands it to the solver warps through a second mbarrier; du becomes c' = du*r [thomas] / d
+//    becomes the pivots d' [bfb] in place in a plane that stays until back-substitution;
+//  * every solver warp keeps its right-hand side in a plane: B lands there by TMA, the forward sweep overwrites it
+//    with y*r [thomas] / x' [bfb], the back-substitution overwrites it with the solution, which leaves by TMA
+//    tensor stores 8 levels at a time. As soon as a chunk's store has been read out, the same lane issues the
+//    load of the NEXT work item's chunk into it; chunk 0 -- freed last, needed first -- alternates between two
+//    "head" slots so that it is loaded a whole item ahead;
+//  * thomas: the factor warp runs the continuant ("ratio") recurrence (no division on its dependent chain, see
+//    tridiag_tma.cu); solver warps have one FMA per level on their chains in both sweeps.
+//  * bfb: the reference's operation order with separately rounded * - / (bit-identical); du for the
+//    back-substitution is read again from L2 through the ring instead of occupying a plane.
+// HBM traffic is the algorithmic minimum when all right-hand sides fit one CTA; otherwise the nrhs/rh groups of a
+// tile run on neighbouring CTAs at the same time and share dl, d, du through L2.
+#include "tridiag_tma.cuh"
+
+namespace ekb {
+
+// bfb factor sweep over one chunk held in registers (ekat_tridiag.hpp:292-303): m = dl(i)/d'(i-1); d'(i) = d(i) - m*du(i-1).
+template <typename R, int CPT, int LB, bool SLOW>
+__device__ __forceinline__ void bfb_factor_chunk(const Vec<R, CPT> (&a)[LB], const Vec<R, CPT> (&b)[LB], const Vec<R, CPT> (&c)[LB],
+                                                 Vec<R, CPT> (&om)[LB], Vec<R, CPT> (&od)[LB], R (&dprev)[CPT], R (&uprev)[CPT],
+                                                 bool first, bool& bad) {
+#pragma unroll
+  for (int u = 0; u < LB; ++u) {
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      R m;
+      if (SLOW) {
+        m = x_div(a[u].v[j], dprev[j]);
+      } else {
+        bool f = false;
+        m = div_spec(a[u].v[j], dprev[j], rcp_refined(dprev[j]), f);
+        if (u == 0) f = f && !first;
+        bad = bad || f;
+      }
+      if (u == 0) m = first ? (R)0 : m;                   // dl(0) is never used (:24-27)
+      const R dc = x_sub(b[u].v[j], x_mul(m, uprev[j]));  // d(i) -= dl(i)*du(i-1)   :301
+      om[u].v[j] = m;
+      od[u].v[j] = dc;
+      dprev[j] = dc;
+      uprev[j] = c[u].v[j];
+    }
+  }
+}
+
+// Phase trace for tuning (variant 7 of ekat_b200_set_tuning selects the instrumented instantiation): per traced CTA
+// (blockIdx 0 and gridDim/2) and work item < kTraceItems, 16 counters in clock64 cycles -- see trace_put call sites.
+constexpr int kTraceItems = 64, kTraceWords = 16;
+__device__ long long g_trace[2 * kTraceItems * kTraceWords];
+__device__ __forceinline__ void trace_put(int it, int idx, long long v) {
+  const int cs = blockIdx.x == 0 ? 0 : (blockIdx.x == gridDim.x / 2 ? 1 : -1);
+  if (cs >= 0 && it < kTraceItems) g_trace[(cs * kTraceItems + it) * kTraceWords + idx] = v;
+}
+
+// grid = persistent CTAs; block = 32 * (rh + 3): warps [0, rh) solve, warp rh factorises, warp rh+1 feeds the ring,
+// warp rh+2 feeds the factor plane.
+// Shared memory: barriers | PC [nslot][LB][32] | PX [rh][nslot][LB][32] | RING [NS][2][LB][32]   (units of V)
+//   nslot = nch + 1: chunk k >= 1 lives in slot k; chunk 0 lives in slot 0 for even items and slot nch for odd ones.
+template <typename R, bool EXACT, int CPT, int RN, bool DBG>
+__global__ void __launch_bounds__(512, 1)
+k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
+                     const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mx, R* __restrict__ X,
+                     int64_t ncol, int nlev, int64_t x_stride, int rh, int ngroups, int nwork, int NS) {
+  using V = Vec<R, CPT>;
+  constexpr int LB = kLB, W = 32 * CPT, CH = LB * 32;
+  constexpr unsigned CHUNK_BYTES = LB * W * sizeof(R);
+  static_assert(LB % RN == 0, "renormalisation interval must divide the chunk");
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nfull = nlev / LB, ntail = nlev - nfull * LB, nch = nfull + (ntail ? 1 : 0), nslot = nch + 1;
+  const int UPT = EXACT ? 2 * nch : nch;  // ring uses per work item
+
+  uint64_t* raw = reinterpret_cast<uint64_t*>(smem_raw);  // [NS]  TMA landed in ring stage
+  uint64_t* ready = raw + NS;                             // [NS]  factor warp transformed the stage
+  uint64_t* freeb = ready + NS;                           // [NS]  all solver warps have read the stage
+  uint64_t* plc = freeb + NS;                             // [nslot] TMA landed in factor-plane slot
+  uint64_t* cfree = plc + nslot;                          // [nslot] all solver warps have read the slot (back-substitution)
+  uint64_t* plx = cfree + nslot;                          // [rh][nslot] TMA landed in a right-hand-side slot
+  const size_t off = ((size_t)(3 * NS + (2 + rh) * nslot) * 8 + 127) & ~(size_t)127;
+  V* PC = reinterpret_cast<V*>(smem_raw + off);
+  V* PX = PC + (size_t)nslot * CH;
+  V* RING = PX + (size_t)rh * nslot * CH;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NS; ++s) {
+      mbar_init(&raw[s], 1);
+      mbar_init(&ready[s], 1);
+      mbar_init(&freeb[s], rh);
+    }
+    for (int k = 0; k < nslot; ++k) {
+      mbar_init(&plc[k], 1);
+      mbar_init(&cfree[k], rh);
+    }
+    for (int k = 0; k < rh * nslot; ++k) mbar_init(&plx[k], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  const int nit = (nwork - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // work items of this CTA
+  auto slot = [&](int k, int it) { return (k == 0 && (it & 1)) ? nch : k; };
+  auto par = [&](int k, int it) { return (unsigned)((k == 0 ? (it >> 1) : it) & 1); };
+  auto item_c0 = [&](int it) { return (int)((((int64_t)blockIdx.x + (int64_t)it * gridDim.x) / ngroups) * W); };
+  auto item_j0 = [&](int it) { return (int)((((int64_t)blockIdx.x + (int64_t)it * gridDim.x) % ngroups) * rh); };
+  const uint64_t pol_stream = l2_policy_evict_first();
+
+  if (warp < rh) {
+    // ================================================================ solver warp: one right-hand side
+    const int jw = warp;
+    V* PXj = PX + (size_t)jw * nslot * CH;
+    uint64_t* plxj = plx + (size_t)jw * nslot;
+    auto load_x = [&](int it2, int k) {  // lane 0: chunk k of work item it2 -> its slot
+      const int sl = slot(k, it2);
+      mbar_expect_tx(&plxj[sl], CHUNK_BYTES);
+      tma_load_2d_hint(PXj + (size_t)sl * CH, &mx, item_c0(it2), (item_j0(it2) + jw) * nlev + k * LB, &plxj[sl], pol_stream);
+    };
+    if (lane == 0) {
+      for (int k = 0; k < nch; ++k) load_x(0, k);
+      if (nit > 1) load_x(1, 0);
+    }
+    for (int it = 0; it < nit; ++it) {
+      const int c0 = item_c0(it), xrow0 = (item_j0(it) + jw) * nlev;
+      const int ubase = it * UPT;
+      const bool has1 = it + 1 < nit, has2 = it + 2 < nit;
+      auto refill = [&](int k) {  // lane 0: slot of chunk k is free again
+        if (k >= 1) {
+          if (has1) load_x(it + 1, k);
+        } else if (has2) {
+          load_x(it + 2, 0);
+        }
+      };
+      // ------------------------------------------------------------ forward sweep
+      R yprev[CPT];
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) yprev[j] = (R)0;
+      long long t0 = 0, w_plx = 0, w_ready = 0, w_store = 0, w_du = 0;
+      if (DBG) t0 = clock64();
+      for (int k = 0; k < nch; ++k) {
+        const int sl = slot(k, it), u0 = ubase + k, s = u0 % NS;
+        long long ta = 0, tb = 0;
+        if (DBG) ta = clock64();
+        mbar_wait(&plxj[sl], par(k, it));
+        if (DBG) tb = clock64();
+        mbar_wait(&ready[s], (unsigned)(u0 / NS) & 1u);
+        if (DBG) {
+          w_plx += tb - ta;
+          w_ready += clock64() - tb;
+        }
+        const V* rm = RING + (size_t)s * 2 * CH + lane;
+        V* px = PXj + (size_t)sl * CH + lane;
+        V m[LB], r[LB], x[LB];
+#pragma unroll
+        for (int u = 0; u < LB; ++u) {
+          m[u] = rm[u * 32];
+          if (!EXACT) r[u] = rm[CH + u * 32];
+          x[u] = px[u * 32];
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&freeb[s]);
+#pragma unroll
+        for (int u = 0; u < LB; ++u) {
+#pragma unroll
+          for (int j = 0; j < CPT; ++j) {
+            if (EXACT) {
+              yprev[j] = x_sub(x[u].v[j], x_mul(m[u].v[j], yprev[j]));  // X(i) -= dl(i)*X(i-1)   :315-316
+              x[u].v[j] = yprev[j];
+            } else {
+              yprev[j] = f_fma(-m[u].v[j], yprev[j], x[u].v[j]);
+              x[u].v[j] = yprev[j] * r[u].v[j];
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < LB; ++u) px[u * 32] = x[u];
+      }
+      long long t1 = 0;
+      if (DBG) t1 = clock64();
+      // ------------------------------------------------------------ back substitution
+      R xv[CPT];
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) xv[j] = (R)0;
+      int pending = -1;  // chunk whose tensor store was committed last (its slot is refilled one step later)
+      for (int jb = 0; jb < nch; ++jb) {
+        const int k = nch - 1 - jb, sl = slot(k, it);
+        int s = 0;
+        if (EXACT) {
+          const int u0 = ubase + nch + jb;
+          s = u0 % NS;
+          long long ta = 0;
+          if (DBG) ta = clock64();
+          mbar_wait(&ready[s], (unsigned)(u0 / NS) & 1u);  // passed on by the factor warp: every ring use completes raw, ready, free in turn
+          mbar_wait(&raw[s], (unsigned)(u0 / NS) & 1u);    // (already complete; direct acquire of the TMA's writes)
+          if (DBG) w_du += clock64() - ta;
+        }
+        const V* bu = RING + (size_t)s * 2 * CH + lane;  // EXACT: du of this chunk, re-read through L2
+        const V* pc = PC + (size_t)sl * CH + lane;
+        V* px = PXj + (size_t)sl * CH + lane;
+        V y[LB], c[LB], ui[LB];
+#pragma unroll
+        for (int u = 0; u < LB; ++u) {
+          y[u] = px[u * 32];
+          c[u] = pc[u * 32];
+          if (EXACT) ui[u] = bu[u * 32];
+        }
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(&cfree[sl]);
+          if (EXACT) mbar_arrive(&freeb[s]);
+        }
+        if (k == nfull) {
+          // partial top chunk (ntail levels): a tensor store would spill into the next right-hand side -> plain stores
+          const int64_t col = (int64_t)c0 + lane * CPT;
+#pragma unroll
+          for (int u = LB - 1; u >= 0; --u) {
+            if (u < ntail) {
+              V o;
+#pragma unroll
+              for (int j = 0; j < CPT; ++j) {
+                if (EXACT) {
+                  const R uu = (u == ntail - 1) ? (R)0 : ui[u].v[j];  // du(nrow-1) is never used (:24-27)
+                  xv[j] = x_div(x_sub(y[u].v[j], x_mul(uu, xv[j])), c[u].v[j]);  // :317-319
+                } else {
+                  xv[j] = f_fma(-c[u].v[j], xv[j], y[u].v[j]);
+                }
+                o.v[j] = xv[j];
+              }
+              R* g = X + (size_t)(xrow0 + k * LB + u) * x_stride + col;
+#pragma unroll
+              for (int j = 0; j < CPT; ++j)
+                if (col + j < ncol) __stcs(g + j, o.v[j]);
+            }
+          }
+          if (lane == 0) refill(k);  // every lane read its part before the __syncwarp above
+        } else {
+          if (EXACT) {
+            if (jb == 0) {  // this chunk ends with the last level
+#pragma unroll
+              for (int j = 0; j < CPT; ++j) ui[LB - 1].v[j] = (R)0;
+            }
+            R sxv[CPT];
+            V ys[LB];
+#pragma unroll
+            for (int j = 0; j < CPT; ++j) sxv[j] = xv[j];
+#pragma unroll
+            for (int u = 0; u < LB; ++u) ys[u] = y[u];
+            bool bad = false;
+            bfb_bwd_chunk<R, CPT, LB, false>(y, c, ui, xv, bad);
+            if (__any_sync(0xffffffffu, bad)) {
+#pragma unroll
+              for (int j = 0; j < CPT; ++j) xv[j] = sxv[j];
+#pragma unroll
+              for (int u = 0; u < LB; ++u) y[u] = ys[u];
+              bfb_bwd_chunk<R, CPT, LB, true>(y, c, ui, xv, bad);
+            }
+          } else {
+#pragma unroll
+            for (int u = LB - 1; u >= 0; --u) {
+#pragma unroll
+              for (int j = 0; j < CPT; ++j) {
+                xv[j] = f_fma(-c[u].v[j], xv[j], y[u].v[j]);
+                y[u].v[j] = xv[j];
+              }
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < LB; ++u) px[u * 32] = y[u];
+          fence_proxy_async();  // generic-proxy writes of this chunk -> visible to the TMA store
+          __syncwarp();
+          if (lane == 0) {
+            long long ta = 0;
+            if (DBG) ta = clock64();
+            tma_store_2d(&mx, c0, xrow0 + k * LB, PXj + (size_t)sl * CH);
+            tma_store_commit();
+            if (pending >= 0) {
+              tma_store_wait_read<1>();  // the previous chunk's store has read its slot
+              refill(pending);
+            }
+            if (DBG) w_store += clock64() - ta;
+          }
+          pending = k;
+        }
+      }
+      if (lane == 0 && pending >= 0) {
+        tma_store_wait_read<0>();
+        refill(pending);
+      }
+      __syncwarp();
+      if (DBG && jw == 0 && lane == 0) {
+        const long long t2 = clock64();
+        trace_put(it, 0, t1 - t0);   // forward sweep, total
+        trace_put(it, 1, w_plx);     //   of which waiting for B chunks
+        trace_put(it, 2, w_ready);   //   of which waiting for the factor warp
+        trace_put(it, 3, t2 - t1);   // back substitution, total
+        trace_put(it, 4, w_store);   //   of which lane 0 in store issue / wait_read / refill
+        trace_put(it, 5, w_du);      //   of which waiting for du (bfb)
+        trace_put(it, 6, t0);        // start time stamp
+      }
+    }
+  } else if (warp == rh) {
+    // ================================================================ factor warp
+    for (int it = 0; it < nit; ++it) {
+      const int ubase = it * UPT;
+      // FAST: q1 = q[i-1], q2 = q[i-2] (ratio form), cp = du[i-1], gp = 1/pivot[i-1].  EXACT: q1 = d'[i-1], cp = du[i-1].
+      R q1[CPT], q2[CPT], cp[CPT], gp[CPT];
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) {
+        q1[j] = (R)1;
+        q2[j] = (R)0;
+        cp[j] = (R)0;
+        gp[j] = (R)0;
+      }
+      long long f0 = 0, w_raw = 0, w_plc = 0;
+      if (DBG) f0 = clock64();
+      for (int k = 0; k < nch; ++k) {
+        const int sl = slot(k, it), u0 = ubase + k, s = u0 % NS;
+        long long ta = 0, tb = 0;
+        if (DBG) ta = clock64();
+        mbar_wait(&raw[s], (unsigned)(u0 / NS) & 1u);
+        if (DBG) tb = clock64();
+        mbar_wait(&plc[sl], par(k, it));
+        if (DBG) {
+          w_raw += tb - ta;
+          w_plc += clock64() - tb;
+        }
+        V* r0 = RING + (size_t)s * 2 * CH + lane;
+        V* r1 = r0 + CH;
+        V* pc = PC + (size_t)sl * CH + lane;
+        V a[LB], b[LB], c[LB], om[LB], o1[LB], oc[LB];
+#pragma unroll
+        for (int u = 0; u < LB; ++u) {
+          a[u] = r0[u * 32];
+          b[u] = EXACT ? pc[u * 32] : r1[u * 32];
+          c[u] = EXACT ? r1[u * 32] : pc[u * 32];
+        }
+        if (EXACT) {
+          R sd[CPT], su[CPT];
+#pragma unroll
+          for (int j = 0; j < CPT; ++j) {
+            sd[j] = q1[j];
+            su[j] = cp[j];
+          }
+          bool bad = false;
+          bfb_factor_chunk<R, CPT, LB, false>(a, b, c, om, oc, q1, cp, k == 0, bad);
+          if (__any_sync(0xffffffffu, bad)) {  // rare operands somewhere in the warp: redo with the full-range division
+#pragma unroll
+            for (int j = 0; j < CPT; ++j) {
+              q1[j] = sd[j];
+              cp[j] = su[j];
+            }
+            bfb_factor_chunk<R, CPT, LB, true>(a, b, c, om, oc, q1, cp, k == 0, bad);
+          }
+        } else {
+          if (k == 0) {  // dl(0) is never used (ekat_tridiag.hpp:24-27) and may hold anything
+#pragma unroll
+            for (int j = 0; j < CPT; ++j) a[0].v[j] = (R)0;
+          }
+#pragma unroll
+          for (int u = 0; u < LB; ++u) {
+#pragma unroll
+            for (int j = 0; j < CPT; ++j) {
+              R q;
+              if (u % RN == 0) q = f_fma(-(a[u].v[j] * cp[j]), q2[j], b[u].v[j]);  // renormalised state: q[i-1] == 1
+              else q = f_fma(b[u].v[j], q1[j], -((a[u].v[j] * cp[j]) * q2[j]));
+              const R rq = t_rcp(q);
+              const R g = (u % RN == 0) ? rq : q1[j] * rq;  // q[i-1]/q[i] = 1/pivot[i]
+              om[u].v[j] = a[u].v[j] * gp[j];               // multiplier dl[i]/pivot[i-1]
+              o1[u].v[j] = g;
+              oc[u].v[j] = (k * LB + u == nlev - 1) ? (R)0 : c[u].v[j] * g;  // du(nrow-1) is never used (:24-27)
+              if ((u + 1) % RN == 0) {
+                q2[j] = g;
+                q1[j] = (R)1;
+              } else {
+                q2[j] = (u % RN == 0) ? (R)1 : q1[j];
+                q1[j] = q;
+              }
+              cp[j] = c[u].v[j];
+              gp[j] = g;
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < LB; ++u) {
+          r0[u * 32] = om[u];
+          if (!EXACT) r1[u * 32] = o1[u];
+          pc[u * 32] = oc[u];
+        }
+        fence_proxy_async();  // these slots are later overwritten by TMA copies
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&ready[s]);
+      }
+      if (DBG && lane == 0) {
+        trace_put(it, 7, clock64() - f0);  // factor warp: forward sweep of this item, total
+        trace_put(it, 8, w_raw);           //   of which waiting for dl, d
+        trace_put(it, 9, w_plc);           //   of which waiting for du / d plane chunks
+        trace_put(it, 10, f0);
+      }
+      if (EXACT) {
+        // the back-substitution's du chunks go through the same ring: hand each one on untouched, so that every
+        // barrier of a stage sees every use (a waiter must never fall two phases behind)
+        for (int jb = 0; jb < nch; ++jb) {
+          const int u0 = ubase + nch + jb, s = u0 % NS;
+          mbar_wait(&raw[s], (unsigned)(u0 / NS) & 1u);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&ready[s]);
+        }
+      }
+    }
+  } else if (warp == rh + 1) {
+    // ================================================================ ring producer
+    if (lane == 0) {
+      for (int it = 0; it < nit; ++it) {
+        const int c0 = item_c0(it), ubase = it * UPT;
+        for (int k = 0; k < UPT; ++k) {
+          const int u0 = ubase + k, s = u0 % NS;
+          if (u0 >= NS) mbar_wait(&freeb[s], (unsigned)(u0 / NS - 1) & 1u);
+          V* st = RING + (size_t)s * 2 * CH;
+          if (k < nch) {
+            mbar_expect_tx(&raw[s], 2u * CHUNK_BYTES);
+            tma_load_2d(st, &mdl, c0, k * LB, &raw[s]);
+            tma_load_2d(st + CH, EXACT ? &mdu : &md, c0, k * LB, &raw[s]);
+          } else {  // EXACT: du of chunk 2*nch-1-k for the back-substitution (an L2 hit)
+            mbar_expect_tx(&raw[s], CHUNK_BYTES);
+            tma_load_2d(st, &mdu, c0, (2 * nch - 1 - k) * LB, &raw[s]);
+          }
+        }
+      }
+    }
+  } else if (warp == rh + 2) {
+    // ================================================================ factor-plane producer
+    if (lane == 0) {
+      auto load_c = [&](int it2, int k) {
+        const int sl = slot(k, it2);
+        mbar_expect_tx(&plc[sl], CHUNK_BYTES);
+        tma_load_2d(PC + (size_t)sl * CH, EXACT ? &md : &mdu, item_c0(it2), k * LB, &plc[sl]);
+      };
+      for (int k = 0; k < nch; ++k) load_c(0, k);
+      if (nit > 1) load_c(1, 0);
+      for (int it = 0; it < nit; ++it) {
+        if (it + 1 < nit)
+          for (int k = nch - 1; k >= 1; --k) {
+            mbar_wait(&cfree[k], (unsigned)it & 1u);
+            load_c(it + 1, k);
+          }
+        if (it + 2 < nit) {
+          mbar_wait(&cfree[slot(0, it)], par(0, it));
+          load_c(it + 2, 0);
+        }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------- host side
+template <typename R, bool EXACT, bool DBG>
+static int launch_shared_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nrhs, int64_t a_stride, int64_t x_stride,
+                             int rh, int ns, size_t smem, cudaStream_t stream, const char* name) {
+  constexpr int CPT = TmaCfg<R>::CPT, RN = EXACT ? 1 : TmaCfg<R>::RN, W = 32 * CPT;
+  CUtensorMap mdl, md, mdu, mx;
+  if (!make_tensor_map_2d<R>(&mdl, dl, ncol, nlev, a_stride, W, kLB) || !make_tensor_map_2d<R>(&md, d, ncol, nlev, a_stride, W, kLB) ||
+      !make_tensor_map_2d<R>(&mdu, du, ncol, nlev, a_stride, W, kLB) ||
+      !make_tensor_map_2d<R>(&mx, X, ncol, (int64_t)nrhs * nlev, x_stride, W, kLB))
+    return EKAT_B200_ERR_UNSUPPORTED;
+  auto k = k_tridiag_tma_shared<R, EXACT, CPT, RN, DBG>;
+  int rc = allow_smem(k, smem);
+  if (rc) return rc;
+  const int ngroups = nrhs / rh;
+  const int64_t ntiles = (ncol + W - 1) / W, nwork = ntiles * ngroups;
+  if (nwork >= (int64_t)1 << 30) return EKAT_B200_ERR_UNSUPPORTED;
+  const int per_sm = (int)((kMaxSmemPerCta + 1024) / (smem + 1024));
+  const int64_t grid = tmin<int64_t>(nwork, (int64_t)kNumSms * tmax(1, per_sm));
+  k<<<(unsigned)grid, 32 * (rh + 3), smem, stream>>>(mdl, md, mdu, mx, X, ncol, nlev, x_stride, rh, ngroups, (int)nwork, ns);
+  note_launch(name);
+  return check_cuda(cudaGetLastError());
+}
+
+// Returns EKAT_B200_ERR_UNSUPPORTED when the operands do not meet TMA's requirements or a tile does not fit on
+// chip; the caller then uses the cp.async kernels.
+template <typename R>
+int tridiag_tma_shared(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nrhs, int64_t a_stride,
+                       int64_t x_stride, cudaStream_t stream) {
+  auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  if (!al(dl) || !al(d) || !al(du) || !al(X) || (a_stride * sizeof(R)) % 16 || (x_stride * sizeof(R)) % 16)
+    return EKAT_B200_ERR_UNSUPPORTED;
+  if (ncol >= (int64_t)1 << 31 || (int64_t)nrhs * nlev >= (int64_t)1 << 31) return EKAT_B200_ERR_UNSUPPORTED;
+  constexpr int CPT = TmaCfg<R>::CPT, W = 32 * CPT;
+  const Tuning tu = tuning();
+  const int nch = (nlev + kLB - 1) / kLB, nslot = nch + 1;
+  const size_t chunk = (size_t)kLB * W * sizeof(R);
+  auto smem_for = [&](int rh, int ns) {
+    const size_t bars = ((size_t)(3 * ns + (2 + rh) * nslot) * 8 + 127) & ~(size_t)127;
+    return bars + (size_t)(1 + rh) * nslot * chunk + (size_t)ns * 2 * chunk;
+  };
+  // right-hand sides per CTA: the largest divisor of nrhs whose planes fit next to a ring of >= 4 stages (>= 2 if none does)
+  int rh = 0, ns = 0;
+  for (int want = 4; want >= 2 && !rh; want -= 2)
+    for (int cand = tmin(nrhs, 13); cand >= 1; --cand) {
+      if (nrhs % cand) continue;
+      if (tu.cols_per_cta > 0 && cand != tu.cols_per_cta) continue;  // tuning override: right-hand sides per CTA
+      int n = 8;
+      while (n >= want && smem_for(cand, n) > kMaxSmemPerCta) --n;
+      if (n >= want) {
+        rh = cand;
+        ns = n;
+        break;
+      }
+    }
+  if (!rh) return EKAT_B200_ERR_UNSUPPORTED;
+  if (tu.prefetch >= 2 && tu.prefetch <= ns) ns = tu.prefetch;  // tuning override: ring stages
+  const size_t smem = smem_for(rh, ns);
+  const bool f64 = sizeof(R) == 8;
+  const char* name = exact ? (f64 ? "tridiag_tma_shared<f64,bfb>" : "tridiag_tma_shared<f32,bfb>")
+                           : (f64 ? "tridiag_tma_shared<f64,thomas>" : "tridiag_tma_shared<f32,thomas>");
+  if (tu.variant == 7)  // instrumented instantiation (phase trace)
+    return exact ? launch_shared_tma<R, true, true>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name)
+                 : launch_shared_tma<R, false, true>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name);
+  return exact ? launch_shared_tma<R, true, false>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name)
+               : launch_shared_tma<R, false, false>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name);
+}
+
+int debug_trace(long long* out, int n) {
+  const int total = 2 * kTraceItems * kTraceWords;
+  if (n > total) n = total;
+  return check_cuda(cudaMemcpyFromSymbol(out, g_trace, (size_t)n * sizeof(long long)));
+}
+
+template int tridiag_tma_shared<double>(bool, double*, double*, double*, double*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
+template int tridiag_tma_shared<float>(bool, float*, float*, float*, float*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
+
+}  // namespace ekb

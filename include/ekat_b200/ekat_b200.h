@@ -260,6 +260,9 @@ const char* ekat_b200_last_kernel(void);
 /* override launch heuristics (0 = automatic): columns per CTA and load-prefetch depth (levels)
  * for the LEV_MAJOR thomas/bfb kernels. Thread-local. For tuning sweeps only. */
 void ekat_b200_set_tuning(int cols_per_cta, int prefetch_levels, int variant);
+/* phase trace of the last instrumented launch (variant 7) of the persistent shared-matrix kernel: copies up to
+ * n int64 words (2 traced CTAs x 64 work items x 16 counters, clock cycles) to the HOST buffer `out`. Tuning only. */
+int ekat_b200_debug_trace(int64_t* out, int n);
 
 #ifdef __cplusplus
 }

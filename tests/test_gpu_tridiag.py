@@ -229,3 +229,22 @@ def test_full_size_configs_properties(cuda, port, dt):
             for lo, hi in [(0, ncol // 3), (ncol // 3, ncol // 2 + 7), (ncol // 2 + 7, ncol)]:
                 T.checksum(X[:, :, lo:hi], out=parts)
             assert whole == int(parts.item())
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+@pytest.mark.parametrize("solver", ["thomas", "bfb"])
+def test_shared_matrix_persistent_many_items(cuda, port, dt, solver):
+    """One matrix, many right-hand sides (BASELINE config 4's shape) at a column count that gives every persistent
+    CTA of the TMA kernel several work items, so the cross-item prefetch (head slots, ring wrap-around, refills
+    behind the tensor stores) is exercised; plus ragged level counts and right-hand-side counts with 1..3 groups."""
+    npdt, _ = DT[dt]
+    W = 32 if dt == "f64" else 64
+    for nrow, nrhs, ncol in [(128, 10, 148 * W * 3 + 5), (72, 10, 148 * W * 2 + W + 1), (43, 4, 148 * W * 4 + 7),
+                             (129, 6, 148 * W * 2 + 3), (5, 3, 148 * W * 5 + 9), (8, 2, 148 * W * 3)]:
+        A, B = port.fill_tridiag(npdt, ncol, nrow, 1, nrhs, col0=11)
+        want = port.tridiag(solver, A.copy(), B.copy())
+        got, Aout = run_gpu(solver, A, B, ekat_b200.LEV_MAJOR, cuda, pad=(-ncol) % 4)  # TMA needs 16-byte pitches
+        from ekat_b200._lib import lib
+        assert lib().ekat_b200_last_kernel().decode().startswith("tridiag_tma_shared"), lib().ekat_b200_last_kernel()
+        check(solver, got, want, npdt, (dt, nrow, nrhs, ncol))
+        assert bits_equal(Aout, A)

@@ -143,7 +143,10 @@ if __name__ == "__main__":
         li_case("f64", 345600, 72, 128, 1, nf=4)
     if "multi" in what:
         for s in ("thomas", "bfb"):
-            tridiag_case(s, "f64", 345600, 128, 1, 10, tunings=[(0, 0, 0), (8, 0, 0), (16, 0, 0)])
+            tridiag_case(s, "f64", 345600, 128, 1, 10, tunings=[(0, 0, 0), (5, 3, 0), (2, 8, 0), (1, 8, 0), (0, 0, 1)])
+            tridiag_case(s, "f32", 345600, 128, 1, 10)
+            tridiag_case(s, "f64", 1572864, 128, 1, 10, tag="config 4")
+            tridiag_case(s, "f64", 345600, 72, 1, 10)
             tridiag_case(s, "f64", 345600, 128, 10, 10)
         tridiag_case("cr", "f64", 100000, 128, 1, 10)
     if "col" in what:
