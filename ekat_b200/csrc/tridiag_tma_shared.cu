@@ -71,7 +71,9 @@ __device__ __forceinline__ void trace_put(int it, int idx, long long v) {
 // grid = persistent CTAs; block = 32 * (rh + 3): warps [0, rh) solve, warp rh factorises, warp rh+1 feeds the ring,
 // warp rh+2 feeds the factor plane.
 // Shared memory: barriers | PC [nslot][LB][32] | PX [rh][nslot][LB][32] | RING [NS][2][LB][32]   (units of V)
-//   nslot = nch + 1: chunk k >= 1 lives in slot k; chunk 0 lives in slot 0 for even items and slot nch for odd ones.
+//   Chunk k of a plane lives in slot k for even work items and in slot nch-1-k for odd ones: the back-substitution
+//   frees slots top chunk first, which is exactly the order in which the next item's forward sweep needs them, so
+//   every chunk of the next item is requested a whole sweep before it is used and no slot is double-buffered.
 template <typename R, bool EXACT, int CPT, int RN, bool DBG>
 __global__ void __launch_bounds__(512, 1)
 k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
@@ -83,7 +85,7 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
   static_assert(LB % RN == 0, "renormalisation interval must divide the chunk");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int nfull = nlev / LB, ntail = nlev - nfull * LB, nch = nfull + (ntail ? 1 : 0), nslot = nch + 1;
+  const int nfull = nlev / LB, ntail = nlev - nfull * LB, nch = nfull + (ntail ? 1 : 0), nslot = nch;
   const int UPT = EXACT ? 2 * nch : nch;  // ring uses per work item
 
   uint64_t* raw = reinterpret_cast<uint64_t*>(smem_raw);  // [NS]  TMA landed in ring stage
@@ -113,10 +115,20 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
   __syncthreads();
 
   const int nit = (nwork - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // work items of this CTA
-  auto slot = [&](int k, int it) { return (k == 0 && (it & 1)) ? nch : k; };
-  auto par = [&](int k, int it) { return (unsigned)((k == 0 ? (it >> 1) : it) & 1); };
-  auto item_c0 = [&](int it) { return (int)((((int64_t)blockIdx.x + (int64_t)it * gridDim.x) / ngroups) * W); };
-  auto item_j0 = [&](int it) { return (int)((((int64_t)blockIdx.x + (int64_t)it * gridDim.x) % ngroups) * rh); };
+  auto slot = [&](int k, int it) { return (it & 1) ? nch - 1 - k : k; };
+  auto par = [&](int, int it) { return (unsigned)(it & 1); };  // every slot is filled once per work item
+  // work item -> (first column of its tile, first right-hand side of its group); nwork < 2^30, so 32-bit arithmetic
+  auto item_c0 = [&](int it) { return (int)(((unsigned)blockIdx.x + (unsigned)it * gridDim.x) / (unsigned)ngroups) * W; };
+  auto item_j0 = [&](int it) { return (int)(((unsigned)blockIdx.x + (unsigned)it * gridDim.x) % (unsigned)ngroups) * rh; };
+  // ring position of a role: stage and phase parity of the use it is at, advanced use by use (no division per chunk)
+  int rs = 0;
+  unsigned rph = 0;
+  auto ring_advance = [&]() {
+    if (++rs == NS) {
+      rs = 0;
+      rph ^= 1u;
+    }
+  };
   const uint64_t pol_stream = l2_policy_evict_first();
 
   if (warp < rh) {
@@ -124,43 +136,40 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
     const int jw = warp;
     V* PXj = PX + (size_t)jw * nslot * CH;
     uint64_t* plxj = plx + (size_t)jw * nslot;
-    auto load_x = [&](int it2, int k) {  // lane 0: chunk k of work item it2 -> its slot
+    auto load_x = [&](int it2, int k, int c0_2, int xrow_2) {  // lane 0: chunk k of work item it2 -> its slot
       const int sl = slot(k, it2);
       mbar_expect_tx(&plxj[sl], CHUNK_BYTES);
-      tma_load_2d_hint(PXj + (size_t)sl * CH, &mx, item_c0(it2), (item_j0(it2) + jw) * nlev + k * LB, &plxj[sl], pol_stream);
+      tma_load_2d_hint(PXj + (size_t)sl * CH, &mx, c0_2, xrow_2 + k * LB, &plxj[sl], pol_stream);
     };
     if (lane == 0) {
-      for (int k = 0; k < nch; ++k) load_x(0, k);
-      if (nit > 1) load_x(1, 0);
+      for (int k = 0; k < nch; ++k) load_x(0, k, item_c0(0), (item_j0(0) + jw) * nlev);
     }
     for (int it = 0; it < nit; ++it) {
       const int c0 = item_c0(it), xrow0 = (item_j0(it) + jw) * nlev;
-      const int ubase = it * UPT;
-      const bool has1 = it + 1 < nit, has2 = it + 2 < nit;
-      auto refill = [&](int k) {  // lane 0: slot of chunk k is free again
-        if (k >= 1) {
-          if (has1) load_x(it + 1, k);
-        } else if (has2) {
-          load_x(it + 2, 0);
-        }
+      const bool has1 = it + 1 < nit;
+      const int c0_n1 = item_c0(it + 1), xrow_n1 = (item_j0(it + 1) + jw) * nlev;
+      auto refill = [&](int jb) {  // lane 0: the slot of this item's chunk nch-1-jb is free again: it is the next item's chunk jb
+        if (has1) load_x(it + 1, jb, c0_n1, xrow_n1);
       };
       // ------------------------------------------------------------ forward sweep
       R yprev[CPT];
 #pragma unroll
       for (int j = 0; j < CPT; ++j) yprev[j] = (R)0;
-      long long t0 = 0, w_plx = 0, w_ready = 0, w_store = 0, w_du = 0;
-      if (DBG) t0 = clock64();
+      long long t0 = 0, tl = 0, acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+      if (DBG) t0 = tl = clock64();
+#define EKB_TICK(i)                  \
+  if (DBG) {                         \
+    const long long n_ = clock64();  \
+    acc[i] += n_ - tl;               \
+    tl = n_;                         \
+  }
       for (int k = 0; k < nch; ++k) {
-        const int sl = slot(k, it), u0 = ubase + k, s = u0 % NS;
-        long long ta = 0, tb = 0;
-        if (DBG) ta = clock64();
+        const int sl = slot(k, it), s = rs;
         mbar_wait(&plxj[sl], par(k, it));
-        if (DBG) tb = clock64();
-        mbar_wait(&ready[s], (unsigned)(u0 / NS) & 1u);
-        if (DBG) {
-          w_plx += tb - ta;
-          w_ready += clock64() - tb;
-        }
+        EKB_TICK(0)
+        mbar_wait(&ready[s], rph);
+        EKB_TICK(1)
+        ring_advance();
         const V* rm = RING + (size_t)s * 2 * CH + lane;
         V* px = PXj + (size_t)sl * CH + lane;
         V m[LB], r[LB], x[LB];
@@ -172,6 +181,7 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&freeb[s]);
+        EKB_TICK(2)
 #pragma unroll
         for (int u = 0; u < LB; ++u) {
 #pragma unroll
@@ -187,41 +197,45 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         }
 #pragma unroll
         for (int u = 0; u < LB; ++u) px[u * 32] = x[u];
+        EKB_TICK(3)
       }
-      long long t1 = 0;
-      if (DBG) t1 = clock64();
       // ------------------------------------------------------------ back substitution
       R xv[CPT];
 #pragma unroll
       for (int j = 0; j < CPT; ++j) xv[j] = (R)0;
-      int pending = -1;  // chunk whose tensor store was committed last (its slot is refilled one step later)
+      // tensor stores are committed one per step; a slot is refilled kSD steps after its store was committed, when
+      // wait_group.read<kSD> no longer has to wait for it
+      constexpr int kSD = 3;
+      const int jb0 = ntail ? 1 : 0;  // the partial top chunk (step 0) leaves by plain stores
       for (int jb = 0; jb < nch; ++jb) {
         const int k = nch - 1 - jb, sl = slot(k, it);
         int s = 0;
         if (EXACT) {
-          const int u0 = ubase + nch + jb;
-          s = u0 % NS;
-          long long ta = 0;
-          if (DBG) ta = clock64();
-          mbar_wait(&ready[s], (unsigned)(u0 / NS) & 1u);  // passed on by the factor warp: every ring use completes raw, ready, free in turn
-          mbar_wait(&raw[s], (unsigned)(u0 / NS) & 1u);    // (already complete; direct acquire of the TMA's writes)
-          if (DBG) w_du += clock64() - ta;
+          s = rs;
+          mbar_wait(&ready[s], rph);  // passed on by the factor warp: every ring use completes raw, ready, free in turn
+          mbar_wait(&raw[s], rph);    // (already complete; direct acquire of the TMA's writes)
+          ring_advance();
         }
+        EKB_TICK(4)
         const V* bu = RING + (size_t)s * 2 * CH + lane;  // EXACT: du of this chunk, re-read through L2
         const V* pc = PC + (size_t)sl * CH + lane;
         V* px = PXj + (size_t)sl * CH + lane;
-        V y[LB], c[LB], ui[LB];
+        V y[LB], c[LB], ui[LB], rr[LB];
 #pragma unroll
         for (int u = 0; u < LB; ++u) {
           y[u] = px[u * 32];
           c[u] = pc[u * 32];
-          if (EXACT) ui[u] = bu[u * 32];
+          if (EXACT) {
+            ui[u] = bu[u * 32];
+            rr[u] = bu[CH + u * 32];  // rcp_refined(d') from the factor warp
+          }
         }
         __syncwarp();
         if (lane == 0) {
           mbar_arrive(&cfree[sl]);
           if (EXACT) mbar_arrive(&freeb[s]);
         }
+        EKB_TICK(5)
         if (k == nfull) {
           // partial top chunk (ntail levels): a tensor store would spill into the next right-hand side -> plain stores
           const int64_t col = (int64_t)c0 + lane * CPT;
@@ -245,7 +259,7 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
                 if (col + j < ncol) __stcs(g + j, o.v[j]);
             }
           }
-          if (lane == 0) refill(k);  // every lane read its part before the __syncwarp above
+          if (lane == 0) refill(jb);  // every lane read its part before the __syncwarp above
         } else {
           if (EXACT) {
             if (jb == 0) {  // this chunk ends with the last level
@@ -259,7 +273,15 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
 #pragma unroll
             for (int u = 0; u < LB; ++u) ys[u] = y[u];
             bool bad = false;
-            bfb_bwd_chunk<R, CPT, LB, false>(y, c, ui, xv, bad);
+#pragma unroll
+            for (int u = LB - 1; u >= 0; --u) {
+#pragma unroll
+              for (int j = 0; j < CPT; ++j) {
+                const R num = x_sub(y[u].v[j], x_mul(ui[u].v[j], xv[j]));  // X(i-1) - du(i-1)*X(i)   :318-319
+                xv[j] = div_spec(num, c[u].v[j], rr[u].v[j], bad);
+                y[u].v[j] = xv[j];
+              }
+            }
             if (__any_sync(0xffffffffu, bad)) {
 #pragma unroll
               for (int j = 0; j < CPT; ++j) xv[j] = sxv[j];
@@ -279,42 +301,38 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
           }
 #pragma unroll
           for (int u = 0; u < LB; ++u) px[u * 32] = y[u];
+          EKB_TICK(6)
           fence_proxy_async();  // generic-proxy writes of this chunk -> visible to the TMA store
           __syncwarp();
+          EKB_TICK(7)
           if (lane == 0) {
-            long long ta = 0;
-            if (DBG) ta = clock64();
             tma_store_2d(&mx, c0, xrow0 + k * LB, PXj + (size_t)sl * CH);
             tma_store_commit();
-            if (pending >= 0) {
-              tma_store_wait_read<1>();  // the previous chunk's store has read its slot
-              refill(pending);
+            if (jb - jb0 >= kSD) {
+              tma_store_wait_read<kSD>();  // the store committed kSD steps ago has read its slot
+              refill(jb - kSD);
             }
-            if (DBG) w_store += clock64() - ta;
           }
-          pending = k;
+          EKB_TICK(8)
         }
       }
-      if (lane == 0 && pending >= 0) {
+      if (lane == 0) {
         tma_store_wait_read<0>();
-        refill(pending);
+        for (int jb = tmax(jb0, nch - kSD); jb < nch; ++jb) refill(jb);
       }
       __syncwarp();
       if (DBG && jw == 0 && lane == 0) {
-        const long long t2 = clock64();
-        trace_put(it, 0, t1 - t0);   // forward sweep, total
-        trace_put(it, 1, w_plx);     //   of which waiting for B chunks
-        trace_put(it, 2, w_ready);   //   of which waiting for the factor warp
-        trace_put(it, 3, t2 - t1);   // back substitution, total
-        trace_put(it, 4, w_store);   //   of which lane 0 in store issue / wait_read / refill
-        trace_put(it, 5, w_du);      //   of which waiting for du (bfb)
-        trace_put(it, 6, t0);        // start time stamp
+        // forward: 0 wait for B chunk, 1 wait for factor warp, 2 shared loads + release, 3 recurrence + shared stores
+        // backward: 4 wait for du (bfb), 5 shared loads + release, 6 recurrence + shared stores, 7 proxy fence + warp
+        // sync, 8 lane 0: tensor store, wait for the previous store's read, refill
+        for (int i = 0; i < 9; ++i) trace_put(it, i, acc[i]);
+        trace_put(it, 9, t0);  // start time stamp
       }
+#undef EKB_TICK
     }
   } else if (warp == rh) {
     // ================================================================ factor warp
     for (int it = 0; it < nit; ++it) {
-      const int ubase = it * UPT;
       // FAST: q1 = q[i-1], q2 = q[i-2] (ratio form), cp = du[i-1], gp = 1/pivot[i-1].  EXACT: q1 = d'[i-1], cp = du[i-1].
       R q1[CPT], q2[CPT], cp[CPT], gp[CPT];
 #pragma unroll
@@ -327,10 +345,11 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
       long long f0 = 0, w_raw = 0, w_plc = 0;
       if (DBG) f0 = clock64();
       for (int k = 0; k < nch; ++k) {
-        const int sl = slot(k, it), u0 = ubase + k, s = u0 % NS;
+        const int sl = slot(k, it), s = rs;
         long long ta = 0, tb = 0;
         if (DBG) ta = clock64();
-        mbar_wait(&raw[s], (unsigned)(u0 / NS) & 1u);
+        mbar_wait(&raw[s], rph);
+        ring_advance();
         if (DBG) tb = clock64();
         mbar_wait(&plc[sl], par(k, it));
         if (DBG) {
@@ -404,17 +423,34 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         if (lane == 0) mbar_arrive(&ready[s]);
       }
       if (DBG && lane == 0) {
-        trace_put(it, 7, clock64() - f0);  // factor warp: forward sweep of this item, total
-        trace_put(it, 8, w_raw);           //   of which waiting for dl, d
-        trace_put(it, 9, w_plc);           //   of which waiting for du / d plane chunks
-        trace_put(it, 10, f0);
+        trace_put(it, 10, clock64() - f0);  // factor warp: forward sweep of this item, total
+        trace_put(it, 11, w_raw);           //   of which waiting for dl, d
+        trace_put(it, 12, w_plc);           //   of which waiting for du / d plane chunks
+        trace_put(it, 13, f0);
       }
       if (EXACT) {
         // the back-substitution's du chunks go through the same ring: hand each one on untouched, so that every
         // barrier of a stage sees every use (a waiter must never fall two phases behind)
+        // ... and carry, in their second half, the refined reciprocals of this chunk's pivots (the part of the IEEE
+        // division that does not depend on the right-hand side, common.cuh), computed once here instead of once per
+        // solver warp
         for (int jb = 0; jb < nch; ++jb) {
-          const int u0 = ubase + nch + jb, s = u0 % NS;
-          mbar_wait(&raw[s], (unsigned)(u0 / NS) & 1u);
+          const int s = rs, sl = slot(nch - 1 - jb, it);
+          const V* pc = PC + (size_t)sl * CH + lane;
+          V* r1 = RING + (size_t)s * 2 * CH + CH + lane;
+          V dd[LB];
+#pragma unroll
+          for (int u = 0; u < LB; ++u) dd[u] = pc[u * 32];
+#pragma unroll
+          for (int u = 0; u < LB; ++u) {
+#pragma unroll
+            for (int j = 0; j < CPT; ++j) dd[u].v[j] = rcp_refined(dd[u].v[j]);
+          }
+          mbar_wait(&raw[s], rph);  // du has landed in the first half; the stage is ours until `ready`
+          ring_advance();
+#pragma unroll
+          for (int u = 0; u < LB; ++u) r1[u * 32] = dd[u];
+          fence_proxy_async();
           __syncwarp();
           if (lane == 0) mbar_arrive(&ready[s]);
         }
@@ -423,11 +459,14 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
   } else if (warp == rh + 1) {
     // ================================================================ ring producer
     if (lane == 0) {
+      bool wrapped = false;
       for (int it = 0; it < nit; ++it) {
-        const int c0 = item_c0(it), ubase = it * UPT;
+        const int c0 = item_c0(it);
         for (int k = 0; k < UPT; ++k) {
-          const int u0 = ubase + k, s = u0 % NS;
-          if (u0 >= NS) mbar_wait(&freeb[s], (unsigned)(u0 / NS - 1) & 1u);
+          const int s = rs;
+          if (wrapped) mbar_wait(&freeb[s], rph ^ 1u);  // the use one lap earlier has been read by every solver warp
+          ring_advance();
+          if (rs == 0) wrapped = true;
           V* st = RING + (size_t)s * 2 * CH;
           if (k < nch) {
             mbar_expect_tx(&raw[s], 2u * CHUNK_BYTES);
@@ -449,18 +488,11 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         tma_load_2d(PC + (size_t)sl * CH, EXACT ? &md : &mdu, item_c0(it2), k * LB, &plc[sl]);
       };
       for (int k = 0; k < nch; ++k) load_c(0, k);
-      if (nit > 1) load_c(1, 0);
-      for (int it = 0; it < nit; ++it) {
-        if (it + 1 < nit)
-          for (int k = nch - 1; k >= 1; --k) {
-            mbar_wait(&cfree[k], (unsigned)it & 1u);
-            load_c(it + 1, k);
-          }
-        if (it + 2 < nit) {
-          mbar_wait(&cfree[slot(0, it)], par(0, it));
-          load_c(it + 2, 0);
+      for (int it = 0; it + 1 < nit; ++it)
+        for (int jb = 0; jb < nch; ++jb) {  // the slot of this item's chunk nch-1-jb becomes the next item's chunk jb
+          mbar_wait(&cfree[slot(nch - 1 - jb, it)], par(0, it));
+          load_c(it + 1, jb);
         }
-      }
     }
   }
 }
@@ -499,7 +531,7 @@ int tridiag_tma_shared(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int n
   if (ncol >= (int64_t)1 << 31 || (int64_t)nrhs * nlev >= (int64_t)1 << 31) return EKAT_B200_ERR_UNSUPPORTED;
   constexpr int CPT = TmaCfg<R>::CPT, W = 32 * CPT;
   const Tuning tu = tuning();
-  const int nch = (nlev + kLB - 1) / kLB, nslot = nch + 1;
+  const int nch = (nlev + kLB - 1) / kLB, nslot = nch;
   const size_t chunk = (size_t)kLB * W * sizeof(R);
   auto smem_for = [&](int rh, int ns) {
     const size_t bars = ((size_t)(3 * ns + (2 + rh) * nslot) * 8 + 127) & ~(size_t)127;

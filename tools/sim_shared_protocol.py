@@ -37,9 +37,11 @@ class Bar:
 
 
 class Sim:
+    SD = 3
+
     def __init__(self, rh, nch, NS, nit, exact, rng):
         self.rh, self.nch, self.NS, self.nit, self.exact, self.rng = rh, nch, NS, nit, exact, rng
-        self.nslot = nch + 1
+        self.nslot = nch
         self.UPT = 2 * nch if exact else nch
         self.raw = [Bar(1) for _ in range(NS)]
         self.ready = [Bar(1) for _ in range(NS)]
@@ -56,10 +58,10 @@ class Sim:
         self.stored = set()
 
     def slot(self, k, it):
-        return self.nch if (k == 0 and (it & 1)) else k
+        return self.nch - 1 - k if (it & 1) else k
 
     def par(self, k, it):
-        return ((it >> 1) if k == 0 else it) & 1
+        return it & 1
 
     # ---- async engine
     def tma_load(self, where, idx, tag, bar, nbytes, guard, after=None):
@@ -103,19 +105,14 @@ class Sim:
         self._store_slots.setdefault(j, [])
         for k in range(nch):
             load_x(0, k)
-        if nit > 1:
-            load_x(1, 0)
         yield None
         for it in range(nit):
             ubase = it * self.UPT
-            has1, has2 = it + 1 < nit, it + 2 < nit
+            has1 = it + 1 < nit
 
-            def refill(k):
-                if k >= 1:
-                    if has1:
-                        load_x(it + 1, k)
-                elif has2:
-                    load_x(it + 2, 0)
+            def refill(jb):
+                if has1:
+                    load_x(it + 1, jb)
             for k in range(nch):
                 sl, u0 = self.slot(k, it), ubase + k
                 s = u0 % NS
@@ -129,7 +126,8 @@ class Sim:
                 self.freeb[s].arrive()
                 yield None
                 PX[sl] = ("Y", it, k)
-            pending = -1
+            SD = self.SD
+            jb0 = 1 if self.nfull_partial >= 0 else 0
             for jb in range(nch):
                 k = nch - 1 - jb
                 sl = self.slot(k, it)
@@ -140,6 +138,7 @@ class Sim:
                     yield lambda s=s, u0=u0: self.ready[s].passed((u0 // NS) & 1)
                     yield lambda s=s, u0=u0: self.raw[s].passed((u0 // NS) & 1)
                     assert self.RING[s][0] == ("du", it, k), f"bwd du ring holds {self.RING[s][0]} want it{it} k{k}"
+                    assert self.RING[s][1] == ("rr", it, k), f"bwd rr ring holds {self.RING[s][1]} want it{it} k{k}"
                 assert PX[sl] == ("Y", it, k)
                 assert self.PC[sl] == ("C'", it, k), f"solver {j} bwd it{it} k{k}: PC holds {self.PC[sl]}"
                 self.pc_readers[sl] -= 1
@@ -151,20 +150,19 @@ class Sim:
                 if k == self.nfull_partial:
                     PX[sl] = ("S", it, k)
                     self.stored.add((j, it, k))
-                    refill(k)
+                    refill(jb)
                 else:
                     PX[sl] = ("S", it, k)
                     flagpos = len(self.store_groups[j])
                     self.tma_store(j, sl, ("S", it, k))
                     self._store_slots[j].append((self.store_groups[j][flagpos], sl))
-                    if pending >= 0:
-                        yield lambda: self.stores_read(j, 1)
-                        refill(pending)
-                    pending = k
+                    if jb - jb0 >= SD:
+                        yield lambda: self.stores_read(j, SD)
+                        refill(jb - SD)
                 yield None
-            if pending >= 0:
-                yield lambda: self.stores_read(j, 0)
-                refill(pending)
+            yield lambda: self.stores_read(j, 0)
+            for jb in range(max(jb0, nch - SD), nch):
+                refill(jb)
 
     def factor(self):
         nch, NS = self.nch, self.NS
@@ -191,7 +189,11 @@ class Sim:
                 for jb in range(nch):
                     u0 = ubase + nch + jb
                     s = u0 % NS
+                    sl = self.slot(nch - 1 - jb, it)
+                    assert self.PC[sl] == ("C'", it, nch - 1 - jb), f"factor bwd it{it} jb{jb}: PC holds {self.PC[sl]}"
                     yield lambda s=s, u0=u0: self.raw[s].passed((u0 // NS) & 1)
+                    assert self.ring_readers[s] == self.rh or True
+                    self.RING[s][1] = ("rr", it, nch - 1 - jb)
                     self.ready[s].arrive()
                     yield None
 
@@ -232,18 +234,12 @@ class Sim:
             self.tma_load(self.PC, sl, ("C", it2, k), self.plc[sl], 1, guard)
         for k in range(nch):
             load_c(0, k)
-        if self.nit > 1:
-            load_c(1, 0)
         yield None
-        for it in range(self.nit):
-            if it + 1 < self.nit:
-                for k in range(nch - 1, 0, -1):
-                    yield lambda k=k, it=it: self.cfree[k].passed(it & 1)
-                    load_c(it + 1, k)
-            if it + 2 < self.nit:
-                sl = self.slot(0, it)
-                yield lambda sl=sl, it=it: self.cfree[sl].passed(self.par(0, it))
-                load_c(it + 2, 0)
+        for it in range(self.nit - 1):
+            for jb in range(nch):
+                sl = self.slot(nch - 1 - jb, it)
+                yield lambda sl=sl, it=it: self.cfree[sl].passed(it & 1)
+                load_c(it + 1, jb)
             yield None
 
     def run(self, partial_tail):
