@@ -329,7 +329,7 @@ int tridiag_levmajor(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nle
     const int rc = tridiag_tma<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }
-  if (nA == 1 && nrhs > 1 && !clobber && (tuning().variant == 0 || tuning().variant == 7)) {
+  if (nA == 1 && nrhs > 1 && !clobber && (tuning().variant == 0 || tuning().variant == 7 || tuning().variant == 8)) {
     const int rc = tridiag_tma_shared<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }

@@ -78,7 +78,7 @@ template <typename R, bool EXACT, int CPT, int RN, bool DBG>
 __global__ void __launch_bounds__(512, 1)
 k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
                      const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mx, R* __restrict__ X,
-                     int64_t ncol, int nlev, int64_t x_stride, int rh, int ngroups, int nwork, int NS) {
+                     int64_t ncol, int nlev, int64_t x_stride, int rh, int ngroups, int nwork, int NS, int io) {
   using V = Vec<R, CPT>;
   constexpr int LB = kLB, W = 32 * CPT, CH = LB * 32;
   constexpr unsigned CHUNK_BYTES = LB * W * sizeof(R);
@@ -94,7 +94,8 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
   uint64_t* plc = freeb + NS;                             // [nslot] TMA landed in factor-plane slot
   uint64_t* cfree = plc + nslot;                          // [nslot] all solver warps have read the slot (back-substitution)
   uint64_t* plx = cfree + nslot;                          // [rh][nslot] TMA landed in a right-hand-side slot
-  const size_t off = ((size_t)(3 * NS + (2 + rh) * nslot) * 8 + 127) & ~(size_t)127;
+  uint64_t* xdone = plx + rh * nslot;                     // [rh][nslot] solver warp finished a slot: solution ready to be stored
+  const size_t off = ((size_t)(3 * NS + (2 + 2 * rh) * nslot) * 8 + 127) & ~(size_t)127;
   V* PC = reinterpret_cast<V*>(smem_raw + off);
   V* PX = PC + (size_t)nslot * CH;
   V* RING = PX + (size_t)rh * nslot * CH;
@@ -109,7 +110,7 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
       mbar_init(&plc[k], 1);
       mbar_init(&cfree[k], rh);
     }
-    for (int k = 0; k < rh * nslot; ++k) mbar_init(&plx[k], 1);
+    for (int k = 0; k < 2 * rh * nslot; ++k) mbar_init(&plx[k], 1);  // plx and xdone
     fence_mbar_init();
   }
   __syncthreads();
@@ -131,17 +132,25 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
   };
   const uint64_t pol_stream = l2_policy_evict_first();
 
+  // right-hand side jw of the CTA: its plane, its barriers, and the copy of chunk k of work item it2 into its slot.
+  // The copies and the tensor stores of a right-hand side are issued by one thread: lane 0 of its io warp
+  // (warp rh+3+jw) when the CTA has io warps, else lane 0 of the solver warp itself. An issue costs that thread
+  // ~130 cycles (measured), which is why it is taken off the solver warps whenever the block size allows.
+  const int jw = warp < rh ? warp : (warp >= rh + 3 ? warp - rh - 3 : 0);
+  V* PXj = PX + (size_t)jw * nslot * CH;
+  uint64_t* plxj = plx + (size_t)jw * nslot;
+  uint64_t* xdonej = xdone + (size_t)jw * nslot;
+  auto load_x = [&](int it2, int k, int c0_2, int xrow_2) {
+    const int sl = slot(k, it2);
+    mbar_expect_tx(&plxj[sl], CHUNK_BYTES);
+    tma_load_2d_hint(PXj + (size_t)sl * CH, &mx, c0_2, xrow_2 + k * LB, &plxj[sl], pol_stream);
+  };
+  constexpr int kSD = 3;  // a slot is refilled kSD steps after its tensor store was committed (wait_group.read<kSD>)
+  const int jb0 = ntail ? 1 : 0;  // the partial top chunk (back-substitution step 0) leaves by plain stores
+
   if (warp < rh) {
     // ================================================================ solver warp: one right-hand side
-    const int jw = warp;
-    V* PXj = PX + (size_t)jw * nslot * CH;
-    uint64_t* plxj = plx + (size_t)jw * nslot;
-    auto load_x = [&](int it2, int k, int c0_2, int xrow_2) {  // lane 0: chunk k of work item it2 -> its slot
-      const int sl = slot(k, it2);
-      mbar_expect_tx(&plxj[sl], CHUNK_BYTES);
-      tma_load_2d_hint(PXj + (size_t)sl * CH, &mx, c0_2, xrow_2 + k * LB, &plxj[sl], pol_stream);
-    };
-    if (lane == 0) {
+    if (lane == 0 && !io) {
       for (int k = 0; k < nch; ++k) load_x(0, k, item_c0(0), (item_j0(0) + jw) * nlev);
     }
     for (int it = 0; it < nit; ++it) {
@@ -155,7 +164,7 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
       R yprev[CPT];
 #pragma unroll
       for (int j = 0; j < CPT; ++j) yprev[j] = (R)0;
-      long long t0 = 0, tl = 0, acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+      long long t0 = 0, tl = 0, acc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
       if (DBG) t0 = tl = clock64();
 #define EKB_TICK(i)                  \
   if (DBG) {                         \
@@ -203,10 +212,6 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
       R xv[CPT];
 #pragma unroll
       for (int j = 0; j < CPT; ++j) xv[j] = (R)0;
-      // tensor stores are committed one per step; a slot is refilled kSD steps after its store was committed, when
-      // wait_group.read<kSD> no longer has to wait for it
-      constexpr int kSD = 3;
-      const int jb0 = ntail ? 1 : 0;  // the partial top chunk (step 0) leaves by plain stores
       for (int jb = 0; jb < nch; ++jb) {
         const int k = nch - 1 - jb, sl = slot(k, it);
         int s = 0;
@@ -259,7 +264,10 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
                 if (col + j < ncol) __stcs(g + j, o.v[j]);
             }
           }
-          if (lane == 0) refill(jb);  // every lane read its part before the __syncwarp above
+          if (lane == 0) {  // every lane read its part of the slot before the __syncwarp above
+            if (io) mbar_arrive(&xdonej[sl]);
+            else refill(jb);
+          }
         } else {
           if (EXACT) {
             if (jb == 0) {  // this chunk ends with the last level
@@ -305,18 +313,22 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
           fence_proxy_async();  // generic-proxy writes of this chunk -> visible to the TMA store
           __syncwarp();
           EKB_TICK(7)
-          if (lane == 0) {
+          if (lane == 0 && io) mbar_arrive(&xdonej[sl]);  // the io warp stores the slot and refills it
+          if (lane == 0 && !io) {
             tma_store_2d(&mx, c0, xrow0 + k * LB, PXj + (size_t)sl * CH);
+            EKB_TICK(8)
             tma_store_commit();
+            EKB_TICK(9)
             if (jb - jb0 >= kSD) {
               tma_store_wait_read<kSD>();  // the store committed kSD steps ago has read its slot
+              EKB_TICK(10)
               refill(jb - kSD);
             }
+            EKB_TICK(11)
           }
-          EKB_TICK(8)
         }
       }
-      if (lane == 0) {
+      if (lane == 0 && !io) {
         tma_store_wait_read<0>();
         for (int jb = tmax(jb0, nch - kSD); jb < nch; ++jb) refill(jb);
       }
@@ -325,8 +337,9 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         // forward: 0 wait for B chunk, 1 wait for factor warp, 2 shared loads + release, 3 recurrence + shared stores
         // backward: 4 wait for du (bfb), 5 shared loads + release, 6 recurrence + shared stores, 7 proxy fence + warp
         // sync, 8 lane 0: tensor store, wait for the previous store's read, refill
-        for (int i = 0; i < 9; ++i) trace_put(it, i, acc[i]);
-        trace_put(it, 9, t0);  // start time stamp
+        // (lane 0 only) 8 tensor store issue, 9 commit, 10 wait_group.read, 11 refill (expect_tx + tensor load issue)
+        for (int i = 0; i < 12; ++i) trace_put(it, i, acc[i]);
+        trace_put(it, 12, t0);  // start time stamp
       }
 #undef EKB_TICK
     }
@@ -423,10 +436,9 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         if (lane == 0) mbar_arrive(&ready[s]);
       }
       if (DBG && lane == 0) {
-        trace_put(it, 10, clock64() - f0);  // factor warp: forward sweep of this item, total
-        trace_put(it, 11, w_raw);           //   of which waiting for dl, d
-        trace_put(it, 12, w_plc);           //   of which waiting for du / d plane chunks
-        trace_put(it, 13, f0);
+        trace_put(it, 13, clock64() - f0);  // factor warp: forward sweep of this item, total
+        trace_put(it, 14, w_raw);           //   of which waiting for dl, d
+        trace_put(it, 15, w_plc);           //   of which waiting for du / d plane chunks
       }
       if (EXACT) {
         // the back-substitution's du chunks go through the same ring: hand each one on untouched, so that every
@@ -494,6 +506,31 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
           load_c(it + 1, jb);
         }
     }
+  } else if (lane == 0) {
+    // ================================================================ io warp of right-hand side jw (only if io)
+    for (int k = 0; k < nch; ++k) load_x(0, k, item_c0(0), (item_j0(0) + jw) * nlev);
+    for (int it = 0; it < nit; ++it) {
+      const int c0 = item_c0(it), xrow0 = (item_j0(it) + jw) * nlev;
+      const bool has1 = it + 1 < nit;
+      const int c0_n1 = item_c0(it + 1), xrow_n1 = (item_j0(it + 1) + jw) * nlev;
+      for (int jb = 0; jb < nch; ++jb) {
+        const int k = nch - 1 - jb, sl = slot(k, it);
+        mbar_wait(&xdonej[sl], par(0, it));
+        if (k == nfull) {  // partial top chunk: already stored by the solver warp
+          if (has1) load_x(it + 1, jb, c0_n1, xrow_n1);
+        } else {
+          tma_store_2d(&mx, c0, xrow0 + k * LB, PXj + (size_t)sl * CH);
+          tma_store_commit();
+          if (jb - jb0 >= kSD) {
+            tma_store_wait_read<kSD>();
+            if (has1) load_x(it + 1, jb - kSD, c0_n1, xrow_n1);
+          }
+        }
+      }
+      tma_store_wait_read<0>();
+      if (has1)
+        for (int jb = tmax(jb0, nch - kSD); jb < nch; ++jb) load_x(it + 1, jb, c0_n1, xrow_n1);
+    }
   }
 }
 
@@ -515,7 +552,10 @@ static int launch_shared_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, i
   if (nwork >= (int64_t)1 << 30) return EKAT_B200_ERR_UNSUPPORTED;
   const int per_sm = (int)((kMaxSmemPerCta + 1024) / (smem + 1024));
   const int64_t grid = tmin<int64_t>(nwork, (int64_t)kNumSms * tmax(1, per_sm));
-  k<<<(unsigned)grid, 32 * (rh + 3), smem, stream>>>(mdl, md, mdu, mx, X, ncol, nlev, x_stride, rh, ngroups, (int)nwork, ns);
+  // one io warp per solver warp (TMA issue off the solver's critical path) while the block stays within 512 threads
+  const int io = (2 * rh + 3) * 32 <= 512 && tuning().variant != 8 ? 1 : 0;
+  k<<<(unsigned)grid, 32 * (rh + 3 + (io ? rh : 0)), smem, stream>>>(mdl, md, mdu, mx, X, ncol, nlev, x_stride, rh, ngroups,
+                                                                    (int)nwork, ns, io);
   note_launch(name);
   return check_cuda(cudaGetLastError());
 }
@@ -534,7 +574,7 @@ int tridiag_tma_shared(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int n
   const int nch = (nlev + kLB - 1) / kLB, nslot = nch;
   const size_t chunk = (size_t)kLB * W * sizeof(R);
   auto smem_for = [&](int rh, int ns) {
-    const size_t bars = ((size_t)(3 * ns + (2 + rh) * nslot) * 8 + 127) & ~(size_t)127;
+    const size_t bars = ((size_t)(3 * ns + (2 + 2 * rh) * nslot) * 8 + 127) & ~(size_t)127;
     return bars + (size_t)(1 + rh) * nslot * chunk + (size_t)ns * 2 * chunk;
   };
   // right-hand sides per CTA: the largest divisor of nrhs whose planes fit next to a ring of >= 4 stages (>= 2 if none does)

@@ -39,7 +39,8 @@ class Bar:
 class Sim:
     SD = 3
 
-    def __init__(self, rh, nch, NS, nit, exact, rng):
+    def __init__(self, rh, nch, NS, nit, exact, rng, io=False):
+        self.io = io
         self.rh, self.nch, self.NS, self.nit, self.exact, self.rng = rh, nch, NS, nit, exact, rng
         self.nslot = nch
         self.UPT = 2 * nch if exact else nch
@@ -49,6 +50,7 @@ class Sim:
         self.plc = [Bar(1) for _ in range(self.nslot)]
         self.cfree = [Bar(rh) for _ in range(self.nslot)]
         self.plx = [[Bar(1) for _ in range(self.nslot)] for _ in range(rh)]
+        self.xdone = [[Bar(1) for _ in range(self.nslot)] for _ in range(rh)]
         self.PC = [None] * self.nslot
         self.PX = [[None] * self.nslot for _ in range(rh)]
         self.RING = [[None, None] for _ in range(NS)]
@@ -90,21 +92,54 @@ class Sim:
         return all(f[0] for f in g[:len(g) - allow]) if len(g) > allow else True
 
     # ---- roles (generators yield a predicate to wait on, or None to just be rescheduled)
+    def load_x(self, j, it2, k):
+        sl = self.slot(k, it2)
+        # the slot must not have an unread store pending, and the solver must be done with it
+        for f, s2 in self._store_slots[j]:
+            assert f[0] or s2 != sl, f"X load into slot {sl} with an unread store pending"
+        assert self.PX[j][sl] is None or self.PX[j][sl][0] == "S", f"X load over live data {self.PX[j][sl]}"
+        self.plx[j][sl].arrive(tx=1)
+        self.tma_load(self.PX[j], sl, ("B", it2, k), self.plx[j][sl], 1, lambda: None)
+
+    def io_warp(self, j):
+        nch, nit, SD = self.nch, self.nit, self.SD
+        jb0 = 1 if self.nfull_partial >= 0 else 0
+        for k in range(nch):
+            self.load_x(j, 0, k)
+        yield None
+        for it in range(nit):
+            has1 = it + 1 < nit
+            for jb in range(nch):
+                k = nch - 1 - jb
+                sl = self.slot(k, it)
+                yield lambda sl=sl, it=it: self.xdone[j][sl].passed(it & 1)
+                if k == self.nfull_partial:
+                    if has1:
+                        self.load_x(j, it + 1, jb)
+                else:
+                    flagpos = len(self.store_groups[j])
+                    self.tma_store(j, sl, ("S", it, k))
+                    self._store_slots[j].append((self.store_groups[j][flagpos], sl))
+                    if jb - jb0 >= SD:
+                        yield lambda: self.stores_read(j, SD)
+                        if has1:
+                            self.load_x(j, it + 1, jb - SD)
+                yield None
+            yield lambda: self.stores_read(j, 0)
+            if has1:
+                for jb in range(max(jb0, nch - SD), nch):
+                    self.load_x(j, it + 1, jb)
+
     def solver(self, j):
         nch, NS, nit = self.nch, self.NS, self.nit
         PX = self.PX[j]
 
         def load_x(it2, k):
-            sl = self.slot(k, it2)
-            # the slot must not have an unread store pending
-            for f, s2 in self._store_slots[j]:
-                assert f[0] or s2 != sl, f"X load into slot {sl} with an unread store pending"
-            self.plx[j][sl].arrive(tx=1)
-            self.tma_load(PX, sl, ("B", it2, k), self.plx[j][sl], 1, lambda: None)
+            self.load_x(j, it2, k)
 
-        self._store_slots.setdefault(j, [])
-        for k in range(nch):
-            load_x(0, k)
+        if not self.io:
+            for k in range(nch):
+                load_x(0, k)
         yield None
         for it in range(nit):
             ubase = it * self.UPT
@@ -150,7 +185,13 @@ class Sim:
                 if k == self.nfull_partial:
                     PX[sl] = ("S", it, k)
                     self.stored.add((j, it, k))
-                    refill(jb)
+                    if self.io:
+                        self.xdone[j][sl].arrive()
+                    else:
+                        refill(jb)
+                elif self.io:
+                    PX[sl] = ("S", it, k)
+                    self.xdone[j][sl].arrive()
                 else:
                     PX[sl] = ("S", it, k)
                     flagpos = len(self.store_groups[j])
@@ -160,9 +201,10 @@ class Sim:
                         yield lambda: self.stores_read(j, SD)
                         refill(jb - SD)
                 yield None
-            yield lambda: self.stores_read(j, 0)
-            for jb in range(max(jb0, nch - SD), nch):
-                refill(jb)
+            if not self.io:
+                yield lambda: self.stores_read(j, 0)
+                for jb in range(max(jb0, nch - SD), nch):
+                    refill(jb)
 
     def factor(self):
         nch, NS = self.nch, self.NS
@@ -246,8 +288,10 @@ class Sim:
         self.nfull_partial = self.nch - 1 if partial_tail else -1
         self.ring_readers = [0] * self.NS
         self.pc_readers = [0] * self.nslot
-        self._store_slots = {}
+        self._store_slots = {j: [] for j in range(self.rh)}
         roles = [self.solver(j) for j in range(self.rh)] + [self.factor(), self.ring_producer(), self.plane_producer()]
+        if self.io:
+            roles += [self.io_warp(j) for j in range(self.rh)]
         waiting = [None] * len(roles)
         alive = [True] * len(roles)
         steps = 0
@@ -293,7 +337,7 @@ def main(trials=300, seed=1):
         nit = rng.choice([1, 2, 3, 4, 7])
         exact = rng.random() < 0.5
         partial = rng.random() < 0.5
-        Sim(rh, nch, NS, nit, exact, rng).run(partial)
+        Sim(rh, nch, NS, nit, exact, rng, io=rng.random() < 0.6).run(partial)
     return trials
 
 

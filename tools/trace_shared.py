@@ -16,8 +16,8 @@ dev = torch.device("cuda:0")
 ncol = int(sys.argv[1]) if len(sys.argv) > 1 else 345600
 nlev = int(sys.argv[2]) if len(sys.argv) > 2 else 128
 nrhs = int(sys.argv[3]) if len(sys.argv) > 3 else 10
-NAMES = ["f.waitB", "f.waitFactor", "f.lds", "f.math+sts", "b.waitDu", "b.lds", "b.math+sts", "b.fence", "b.lane0", "t_start",
-         "factor", "factor.waitRing", "factor.waitPlane", "factor.t_start"]
+NAMES = ["f.waitB", "f.waitFactor", "f.lds", "f.math+sts", "b.waitDu", "b.lds", "b.math+sts", "b.fence", "b.stg", "b.commit",
+         "b.waitread", "b.refill", "t_start", "factor", "factor.waitRing", "factor.waitPlane"]
 for dt in (torch.float64,):
     dl, d, du, B = T.fill(dt, ncol, nlev, 1, nrhs, device=dev)
     X = B.clone()
@@ -35,7 +35,6 @@ for dt in (torch.float64,):
             tr = buf.reshape(2, 64, 16)
             for c in range(2):
                 sel = tr[c, 8:60]
-                period = np.diff(sel[:, 9]).mean()
+                period = np.diff(sel[:, 12]).mean()
                 print(f"{solver} tuning={tu} cta{c}: item period {period:.0f} cyc | " +
                       " ".join(f"{n}={sel[:, i].mean():.0f}" for i, n in enumerate(NAMES) if not n.endswith("t_start")))
-                print("    factor start - solver fwd start (cyc):", (sel[:, 13] - sel[:, 9]).mean().round())
