@@ -16,6 +16,9 @@ template <typename R>
 int tridiag_tile(int algo, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nA, int nrhs, int64_t a_stride,
                  int64_t x_stride, int layout, unsigned flags, cudaStream_t stream);
 template <typename R>
+int tridiag_tma_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride,
+                   cudaStream_t stream);
+template <typename R>
 int lin_interp(int mode, const R* x1, const R* x2, const R* y1, R* y2, int* indx, const int* indx_in, int64_t ncol,
                int km1, int km2, int64_t pitch1, int64_t pitch2, int nfields, int64_t y1_fstride, int64_t y2_fstride,
                cudaStream_t stream);
@@ -81,6 +84,11 @@ static int tridiag_entry(int solver, R* dl, R* d, R* du, R* X, int64_t ncol, int
   if (solver == SOLVER_CR) return tridiag_tile<R>(2, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, layout, flags, st);
   if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && tuning().variant != 2)
     return tridiag_levmajor<R>(solver == SOLVER_BFB, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, flags, st);
+  if (layout == EKAT_B200_LAYOUT_COL_MAJOR && nA == 1 && nrhs == 1 && !flags && tuning().variant == 0) {
+    // reference layout, one right-hand side: the TMA kernel reads the columns where they lie (tridiag_tma.cu)
+    const int rc = tridiag_tma_cm<R>(solver == SOLVER_BFB, dl, d, du, X, ncol, nlev, a_stride, x_stride, st);
+    if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+  }
   return tridiag_tile<R>(solver == SOLVER_BFB ? 1 : 0, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, layout,
                          flags, st);
 }

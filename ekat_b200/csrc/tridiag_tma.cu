@@ -63,17 +63,43 @@ template bool make_tensor_map_2d<double>(CUtensorMap*, const double*, int64_t, i
 template bool make_tensor_map_2d<float>(CUtensorMap*, const float*, int64_t, int64_t, int64_t, int, int);
 
 // ------------------------------------------------------------------------------------------- the kernel
-// grid = (column tiles, matrices); block = 32 threads. Lane l owns columns c0 + l*CPT .. +CPT-1.
+// Element (level u of a chunk, lane, j-th column of the lane) of a shared-memory chunk of LB levels x W columns.
+//   level-major operands (CM = false): the TMA box is LB rows of W columns -> [u][lane][j], one vector access;
+//   the reference's column-major operands (CM = true: a column's levels are contiguous in memory,
+//   tests/algorithm/tridiag_tests_performance.cpp:181-185): the box is W rows (columns) of LB levels -> [j*32+lane][u].
+//   A row is LB*sizeof(R) = 48 bytes there (TMA needs multiples of 16), i.e. an even number of 8-byte words, so a
+//   level step of the warp is a 2-way (f64) / 4-way (f32) bank conflict -- the price of needing no transpose pass.
+template <typename R, int CPT, int LB, bool CM>
+__device__ __forceinline__ Vec<R, CPT> t_ld(const Vec<R, CPT>* chunk, int u, int lane) {
+  if (!CM) return chunk[u * 32 + lane];
+  Vec<R, CPT> v;
+  const R* e = reinterpret_cast<const R*>(chunk);
+#pragma unroll
+  for (int j = 0; j < CPT; ++j) v.v[j] = e[(j * 32 + lane) * LB + u];
+  return v;
+}
+template <typename R, int CPT, int LB, bool CM>
+__device__ __forceinline__ void t_st(Vec<R, CPT>* chunk, int u, int lane, const Vec<R, CPT>& v) {
+  if (!CM) {
+    chunk[u * 32 + lane] = v;
+    return;
+  }
+  R* e = reinterpret_cast<R*>(chunk);
+#pragma unroll
+  for (int j = 0; j < CPT; ++j) e[(j * 32 + lane) * LB + u] = v.v[j];
+}
+
+// grid = (column tiles, matrices); block = 32 threads. Lane l owns columns c0 + l*CPT .. +CPT-1 (CM: c0 + l + 32*j).
 // Shared memory: [ring barriers NS][plane barriers nch] | planes [level][lane] | rings [stage][LB][lane].
 //   FAST : P0 = du -> c',  P1 = x -> y -> solution;            rings dl, d
 //   EXACT: P0 = d  -> d',  P1 = x -> x' -> solution,  P2 = du;  ring  dl
-template <typename R, bool EXACT, int CPT, int RN, int NS>
+template <typename R, bool EXACT, int CPT, int RN, int NS, int LBT, bool CM>
 __global__ void __launch_bounds__(32)
 k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
               const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mx, R* __restrict__ X,
               int64_t ncol, int nlev, int64_t x_stride, int pd) {
   using V = Vec<R, CPT>;
-  constexpr int LB = kLB, W = 32 * CPT;
+  constexpr int LB = LBT, W = 32 * CPT;
   constexpr unsigned CHUNK_BYTES = LB * W * sizeof(R);
   static_assert(LB % RN == 0, "renormalisation interval must divide the chunk");
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -108,23 +134,28 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
   // which is what lets three bfb CTAs share an SM.
   const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
 
+  // chunk k of a tensor: box coordinates (fastest, slowest) = (columns, levels) or, column-major, (levels, columns)
+  auto load_chunk = [&](void* dst, const CUtensorMap* m, int k, uint64_t* bar, uint64_t pol) {
+    if (CM) tma_load_2d_hint(dst, m, k * LB, c0, bar, pol);
+    else tma_load_2d_hint(dst, m, c0, row0 + k * LB, bar, pol);
+  };
   auto issue_ring = [&](int k) {
     const int s = k % NS;
     mbar_expect_tx(&rbar[s], 2u * CHUNK_BYTES);
-    tma_load_2d_hint(RA + (size_t)s * LB * 32, &mdl, c0, row0 + k * LB, &rbar[s], pol_stream);
-    if (EXACT) tma_load_2d_hint(RB + (size_t)s * LB * 32, &mdu, c0, row0 + k * LB, &rbar[s], pol_keep);
-    else tma_load_2d_hint(RB + (size_t)s * LB * 32, &md, c0, row0 + k * LB, &rbar[s], pol_stream);
+    load_chunk(RA + (size_t)s * LB * 32, &mdl, k, &rbar[s], pol_stream);
+    if (EXACT) load_chunk(RB + (size_t)s * LB * 32, &mdu, k, &rbar[s], pol_keep);
+    else load_chunk(RB + (size_t)s * LB * 32, &md, k, &rbar[s], pol_stream);
   };
   auto issue_plane = [&](int k) {
     const size_t o = (size_t)k * LB * 32;
     mbar_expect_tx(&pbar[k], 2u * CHUNK_BYTES);
-    tma_load_2d_hint(P0 + o, EXACT ? &md : &mdu, c0, row0 + k * LB, &pbar[k], pol_stream);
-    tma_load_2d_hint(P1 + o, &mx, c0, row0 + k * LB, &pbar[k], pol_stream);
+    load_chunk(P0 + o, EXACT ? &md : &mdu, k, &pbar[k], pol_stream);
+    load_chunk(P1 + o, &mx, k, &pbar[k], pol_stream);
   };
   auto issue_back = [&](int j) {  // EXACT: du of chunk nch-1-j for the back-substitution
     const int s = j % (2 * NS);
     mbar_expect_tx(&bbar[s], CHUNK_BYTES);
-    tma_load_2d_hint(RA + (size_t)s * LB * 32, &mdu, c0, row0 + (nch - 1 - j) * LB, &bbar[s], pol_stream);
+    load_chunk(RA + (size_t)s * LB * 32, &mdu, nch - 1 - j, &bbar[s], pol_stream);
   };
   if (lane == 0) {
     const int n0 = pd > NS ? pd : NS;
@@ -148,19 +179,20 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
     const int s = k % NS;
     mbar_wait(&rbar[s], (unsigned)(k / NS) & 1u);
     mbar_wait(&pbar[k], 0u);
-    const V* ra = RA + (size_t)s * LB * 32 + lane;
-    const V* rb = RB + (size_t)s * LB * 32 + lane;
-    V* p0 = P0 + (size_t)k * LB * 32 + lane;
-    V* p1 = P1 + (size_t)k * LB * 32 + lane;
+    const V* ra = RA + (size_t)s * LB * 32;
+    const V* rb = RB + (size_t)s * LB * 32;
+    V* p0 = P0 + (size_t)k * LB * 32;
+    V* p1 = P1 + (size_t)k * LB * 32;
+    auto ld = [&](const V* chunk, int u) { return t_ld<R, CPT, LB, CM>(chunk, u, lane); };
     // stage the whole chunk in registers first: one shared-memory latency per chunk instead of one per level
     // (the in-place plane updates below would otherwise order every level's loads behind the previous stores)
     V a[LB], b[LB], c[LB], x[LB], o0[LB], o1[LB];
 #pragma unroll
     for (int u = 0; u < LB; ++u) {
-      a[u] = ra[u * 32];
-      x[u] = p1[u * 32];
-      b[u] = EXACT ? p0[u * 32] : rb[u * 32];
-      c[u] = EXACT ? rb[u * 32] : p0[u * 32];
+      a[u] = ld(ra, u);
+      x[u] = ld(p1, u);
+      b[u] = EXACT ? ld(p0, u) : ld(rb, u);
+      c[u] = EXACT ? ld(rb, u) : ld(p0, u);
     }
     if (EXACT) {
       R sd[CPT], sx[CPT], su[CPT];
@@ -218,8 +250,8 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
     }
 #pragma unroll
     for (int u = 0; u < LB; ++u) {
-      p0[u * 32] = o0[u];
-      p1[u * 32] = o1[u];
+      t_st<R, CPT, LB, CM>(p0, u, lane, o0[u]);
+      t_st<R, CPT, LB, CM>(p1, u, lane, o1[u]);
     }
     __syncwarp();  // every lane has read ring stage s
     if (lane == 0) {
@@ -232,7 +264,7 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
     V zero;
 #pragma unroll
     for (int j = 0; j < CPT; ++j) zero.v[j] = (R)0;
-    P0[(size_t)(nlev - 1) * 32 + lane] = zero;
+    t_st<R, CPT, LB, CM>(P0 + (size_t)((nlev - 1) / LB) * LB * 32, (nlev - 1) % LB, lane, zero);
   } else if (lane == 0) {
     for (int j = 0; j < 2 * NS && j < nch; ++j) issue_back(j);  // both rings are free now: refill them with du from L2
   }
@@ -243,18 +275,20 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
   for (int j = 0; j < CPT; ++j) xv[j] = (R)0;
   for (int jb = 0; jb < nch; ++jb) {
     const int k = nch - 1 - jb;
-    V* q1p = P1 + (size_t)k * LB * 32 + lane;
-    const V* q0p = P0 + (size_t)k * LB * 32 + lane;
-    const V* bu = RA + (size_t)(jb % (2 * NS)) * LB * 32 + lane;
+    V* q1p = P1 + (size_t)k * LB * 32;
+    const V* q0p = P0 + (size_t)k * LB * 32;
+    const V* bu = RA + (size_t)(jb % (2 * NS)) * LB * 32;
+    auto ld = [&](const V* chunk, int u) { return t_ld<R, CPT, LB, CM>(chunk, u, lane); };
     if (EXACT) mbar_wait(&bbar[jb % (2 * NS)], (unsigned)(jb / (2 * NS)) & 1u);
     if (k == nfull) {
-      // partial top chunk: a tensor store would spill into the next matrix' rows -> plain streaming stores
+      // partial top chunk. Level-major: a tensor store would spill into the next matrix' rows -> plain streaming
+      // stores. Column-major: the box is clipped at the end of the column, so it leaves by tensor store like the rest.
       const int64_t col = (int64_t)c0 + lane * CPT;
       for (int u = ntail - 1; u >= 0; --u) {
-        const V y = q1p[u * 32], m0 = q0p[u * 32];
+        const V y = ld(q1p, u), m0 = ld(q0p, u);
         V o;
         if (EXACT) {
-          V ui = bu[u * 32];
+          V ui = ld(bu, u);
           if (u == ntail - 1) {
 #pragma unroll
             for (int j = 0; j < CPT; ++j) ui.v[j] = (R)0;
@@ -271,18 +305,23 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
             o.v[j] = xv[j];
           }
         }
-        R* g = X + (size_t)(row0 + k * LB + u) * x_stride + col;
+        if (CM) {
+          t_st<R, CPT, LB, CM>(q1p, u, lane, o);
+        } else {
+          R* g = X + (size_t)(row0 + k * LB + u) * x_stride + col;
 #pragma unroll
-        for (int j = 0; j < CPT; ++j)
-          if (col + j < ncol) __stcs(g + j, o.v[j]);
+          for (int j = 0; j < CPT; ++j)
+            if (col + j < ncol) __stcs(g + j, o.v[j]);
+        }
       }
+      if (CM) fence_proxy_async();
     } else {
       V y[LB], m0[LB], ui[LB];
 #pragma unroll
       for (int u = 0; u < LB; ++u) {
-        y[u] = q1p[u * 32];
-        m0[u] = q0p[u * 32];
-        if (EXACT) ui[u] = bu[u * 32];
+        y[u] = ld(q1p, u);
+        m0[u] = ld(q0p, u);
+        if (EXACT) ui[u] = ld(bu, u);
       }
       if (EXACT) {
         if (jb == 0) {  // this chunk ends with the last level
@@ -315,12 +354,15 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
         }
       }
 #pragma unroll
-      for (int u = 0; u < LB; ++u) q1p[u * 32] = y[u];
+      for (int u = 0; u < LB; ++u) t_st<R, CPT, LB, CM>(q1p, u, lane, y[u]);
       fence_proxy_async();  // generic-proxy writes of this chunk -> visible to the TMA store
     }
     __syncwarp();  // every lane has read its du stage / written its part of the chunk
     if (lane == 0) {
-      if (k != nfull) {
+      if (CM) {
+        tma_store_2d(&mx, k * LB, c0, P1 + (size_t)k * LB * 32);
+        tma_store_commit();
+      } else if (k != nfull) {
         tma_store_2d(&mx, c0, row0 + k * LB, P1 + (size_t)k * LB * 32);
         tma_store_commit();
       }
@@ -331,16 +373,36 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
 }
 
 // ------------------------------------------------------------------------------------------- host side
-template <typename R, bool EXACT, int NS>
+// Chunk length and renormalisation interval per layout. Column-major rows are LB*sizeof(R) = 48 bytes (see t_ld).
+template <typename R, bool CM>
+struct TmaGeom {
+  static constexpr int LB = kLB, RN = TmaCfg<R>::RN;
+};
+template <>
+struct TmaGeom<double, true> {
+  static constexpr int LB = 6, RN = 6;
+};
+template <>
+struct TmaGeom<float, true> {
+  static constexpr int LB = 12, RN = 2;
+};
+
+template <typename R, bool EXACT, int NS, bool CM>
 static int launch_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
                       int pd, size_t smem, cudaStream_t stream, const char* name) {
-  constexpr int CPT = TmaCfg<R>::CPT, RN = EXACT ? 1 : TmaCfg<R>::RN, W = 32 * CPT;
+  constexpr int CPT = TmaCfg<R>::CPT, LB = TmaGeom<R, CM>::LB, RN = EXACT ? 1 : TmaGeom<R, CM>::RN, W = 32 * CPT;
   CUtensorMap mdl, md, mdu, mx;
-  const int64_t rows = (int64_t)nmat * nlev;
-  if (!make_tensor_map_2d<R>(&mdl, dl, ncol, rows, a_stride, W, kLB) || !make_tensor_map_2d<R>(&md, d, ncol, rows, a_stride, W, kLB) ||
-      !make_tensor_map_2d<R>(&mdu, du, ncol, rows, a_stride, W, kLB) || !make_tensor_map_2d<R>(&mx, X, ncol, rows, x_stride, W, kLB))
-    return EKAT_B200_ERR_UNSUPPORTED;
-  auto k = k_tridiag_tma<R, EXACT, CPT, RN, NS>;
+  bool ok;
+  if (CM) {  // [ncol][stride] rows of which the first nlev entries are the column: fastest dimension = level
+    ok = make_tensor_map_2d<R>(&mdl, dl, nlev, ncol, a_stride, LB, W) && make_tensor_map_2d<R>(&md, d, nlev, ncol, a_stride, LB, W) &&
+         make_tensor_map_2d<R>(&mdu, du, nlev, ncol, a_stride, LB, W) && make_tensor_map_2d<R>(&mx, X, nlev, ncol, x_stride, LB, W);
+  } else {
+    const int64_t rows = (int64_t)nmat * nlev;
+    ok = make_tensor_map_2d<R>(&mdl, dl, ncol, rows, a_stride, W, LB) && make_tensor_map_2d<R>(&md, d, ncol, rows, a_stride, W, LB) &&
+         make_tensor_map_2d<R>(&mdu, du, ncol, rows, a_stride, W, LB) && make_tensor_map_2d<R>(&mx, X, ncol, rows, x_stride, W, LB);
+  }
+  if (!ok) return EKAT_B200_ERR_UNSUPPORTED;
+  auto k = k_tridiag_tma<R, EXACT, CPT, RN, NS, LB, CM>;
   int rc = allow_smem(k, smem);
   if (rc) return rc;
   dim3 grid((unsigned)((ncol + W - 1) / W), (unsigned)nmat);
@@ -350,18 +412,19 @@ static int launch_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat
 }
 
 // Returns EKAT_B200_ERR_UNSUPPORTED when the operands do not meet TMA's requirements (16-byte aligned bases and
-// pitches, column fits on chip, sizes within tensor-map limits); the caller then uses the cp.async kernels.
-template <typename R>
-int tridiag_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride,
-                int64_t x_stride, cudaStream_t stream) {
+// pitches, column fits on chip, sizes within tensor-map limits); the caller then uses the cp.async / tile kernels.
+template <typename R, bool CM>
+static int run_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride,
+                   int64_t x_stride, cudaStream_t stream) {
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
   if (!al(dl) || !al(d) || !al(du) || !al(X) || (a_stride * sizeof(R)) % 16 || (x_stride * sizeof(R)) % 16)
     return EKAT_B200_ERR_UNSUPPORTED;
   if (ncol >= (int64_t)1 << 31 || (int64_t)nmat * nlev >= (int64_t)1 << 31 || nmat > 65535) return EKAT_B200_ERR_UNSUPPORTED;
-  constexpr int CPT = TmaCfg<R>::CPT, W = 32 * CPT;
+  if (CM && nmat != 1) return EKAT_B200_ERR_UNSUPPORTED;  // several right-hand sides interleave within a column there
+  constexpr int CPT = TmaCfg<R>::CPT, W = 32 * CPT, LB = TmaGeom<R, CM>::LB;
   const Tuning tu = tuning();
-  const int nch = (nlev + kLB - 1) / kLB;
-  const size_t chunk = (size_t)kLB * W * sizeof(R);
+  const int nch = (nlev + LB - 1) / LB;
+  const size_t chunk = (size_t)LB * W * sizeof(R);
   const size_t bars = ((size_t)(12 + nch) * 8 + 127) & ~(size_t)127;
   const size_t planes = (size_t)2 * nch * chunk;
   const int nrings = 2;
@@ -371,19 +434,37 @@ int tridiag_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, in
   if (tu.cols_per_cta == 2 || tu.cols_per_cta == 4) ns = tu.cols_per_cta;  // tuning override: ring stages
   const size_t smem = bars + planes + (size_t)nrings * ns * chunk;
   if (smem > kMaxSmemPerCta) return EKAT_B200_ERR_UNSUPPORTED;
-  int pd = tu.prefetch > 0 ? tu.prefetch : 3;  // plane chunks in flight ahead of the sweep
+  int pd = tu.prefetch > 0 ? tu.prefetch : (CM ? 4 : 3);  // plane chunks in flight ahead of the sweep
   if (pd < 1) pd = 1;
   const bool f64 = sizeof(R) == 8;
-  const char* name = exact ? (f64 ? "tridiag_tma<f64,bfb>" : "tridiag_tma<f32,bfb>")
-                           : (f64 ? "tridiag_tma<f64,thomas>" : "tridiag_tma<f32,thomas>");
+  const char* name = CM ? (exact ? (f64 ? "tridiag_tma_cm<f64,bfb>" : "tridiag_tma_cm<f32,bfb>")
+                                 : (f64 ? "tridiag_tma_cm<f64,thomas>" : "tridiag_tma_cm<f32,thomas>"))
+                        : (exact ? (f64 ? "tridiag_tma<f64,bfb>" : "tridiag_tma<f32,bfb>")
+                                 : (f64 ? "tridiag_tma<f64,thomas>" : "tridiag_tma<f32,thomas>"));
   if (exact)
-    return ns == 2 ? launch_tma<R, true, 2>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name)
-                   : launch_tma<R, true, 4>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name);
-  return ns == 2 ? launch_tma<R, false, 2>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name)
-                 : launch_tma<R, false, 4>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name);
+    return ns == 2 ? launch_tma<R, true, 2, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name)
+                   : launch_tma<R, true, 4, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name);
+  return ns == 2 ? launch_tma<R, false, 2, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name)
+                 : launch_tma<R, false, 4, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name);
+}
+
+// level-major operands: dl,d,du [nmat][nlev][a_stride], X [nmat][nlev][x_stride], columns fastest
+template <typename R>
+int tridiag_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride,
+                int64_t x_stride, cudaStream_t stream) {
+  return run_tma<R, false>(exact, dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, stream);
+}
+// the reference's column-major operands, one matrix and one right-hand side per column: dl,d,du [ncol][a_stride],
+// X [ncol][x_stride], levels fastest
+template <typename R>
+int tridiag_tma_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride,
+                   cudaStream_t stream) {
+  return run_tma<R, true>(exact, dl, d, du, X, ncol, nlev, 1, a_stride, x_stride, stream);
 }
 
 template int tridiag_tma<double>(bool, double*, double*, double*, double*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
 template int tridiag_tma<float>(bool, float*, float*, float*, float*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
+template int tridiag_tma_cm<double>(bool, double*, double*, double*, double*, int64_t, int, int64_t, int64_t, cudaStream_t);
+template int tridiag_tma_cm<float>(bool, float*, float*, float*, float*, int64_t, int, int64_t, int64_t, cudaStream_t);
 
 }  // namespace ekb

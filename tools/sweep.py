@@ -131,6 +131,13 @@ if __name__ == "__main__":
             for s in ("thomas", "bfb"):
                 tridiag_case(s, dt, 345600, 128, tunings=grid)
             tridiag_case("cr", dt, 345600, 128, tunings=[(0, 0, 0), (8, 0, 0), (16, 0, 0), (32, 0, 0)])
+    if "tma" in what:
+        grid = [(0, 0, 0), (2, 2, 0), (2, 5, 0), (2, 8, 0), (2, 16, 0), (4, 4, 0)]
+        for s in ("thomas", "bfb"):
+            tridiag_case(s, "f64", 345600, 128, tunings=grid)
+            tridiag_case(s, "f32", 345600, 128)
+            tridiag_case(s, "f64", 3145728, 128)
+            tridiag_case(s, "f64", 21600, 72)
     if "c1" in what:
         for s in ("thomas", "bfb", "cr"):
             tridiag_case(s, "f64", 21600, 72, tunings=[(0, 0, 0), (16, 8, 0), (16, 16, 0), (32, 8, 0), (64, 16, 0)])
