@@ -48,7 +48,7 @@ static EncodeTiledFn encode_fn() {
 // [nrows][pitch] array of R, of which the first ncol entries of a row are data; box = boxc columns x boxr rows.
 // Columns beyond ncol read as zero and are not written (TMA bounds handling).
 template <typename R>
-bool make_tensor_map_2d(CUtensorMap* m, const R* base, int64_t ncol, int64_t nrows, int64_t pitch, int boxc, int boxr) {
+bool make_tensor_map_2d(CUtensorMap* m, const R* base, int64_t ncol, int64_t nrows, int64_t pitch, int boxc, int boxr, int swizzle64) {
   EncodeTiledFn enc = encode_fn();
   if (!enc) return false;
   const cuuint64_t dims[2] = {(cuuint64_t)ncol, (cuuint64_t)nrows};
@@ -57,25 +57,35 @@ bool make_tensor_map_2d(CUtensorMap* m, const R* base, int64_t ncol, int64_t nro
   const cuuint32_t estr[2] = {1, 1};
   const CUtensorMapDataType dt = sizeof(R) == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
   return enc(m, dt, 2, const_cast<R*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+             swizzle64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
-template bool make_tensor_map_2d<double>(CUtensorMap*, const double*, int64_t, int64_t, int64_t, int, int);
-template bool make_tensor_map_2d<float>(CUtensorMap*, const float*, int64_t, int64_t, int64_t, int, int);
+template bool make_tensor_map_2d<double>(CUtensorMap*, const double*, int64_t, int64_t, int64_t, int, int, int);
+template bool make_tensor_map_2d<float>(CUtensorMap*, const float*, int64_t, int64_t, int64_t, int, int, int);
 
 // ------------------------------------------------------------------------------------------- the kernel
 // Element (level u of a chunk, lane, j-th column of the lane) of a shared-memory chunk of LB levels x W columns.
 //   level-major operands (CM = false): the TMA box is LB rows of W columns -> [u][lane][j], one vector access;
 //   the reference's column-major operands (CM = true: a column's levels are contiguous in memory,
 //   tests/algorithm/tridiag_tests_performance.cpp:181-185): the box is W rows (columns) of LB levels -> [j*32+lane][u].
-//   A row is LB*sizeof(R) = 48 bytes there (TMA needs multiples of 16), i.e. an even number of 8-byte words, so a
-//   level step of the warp is a 2-way (f64) / 4-way (f32) bank conflict -- the price of needing no transpose pass.
+//   A level step of the warp then strides by the row length, which TMA wants in multiples of 16 bytes -- never an
+//   odd number of words, so some bank conflict is the price of needing no transpose pass. Rows of 64 bytes with the
+//   TMA's 64-byte swizzle (16-byte unit index XOR bits 7-8 of the address, i.e. XOR (row/2)%4) spread a level over
+//   8 of the 16 bank pairs (f64: 4 wavefronts instead of 2); unswizzled 48-byte rows do the same for f32.
+template <int BYTES>
+__device__ __forceinline__ int cm_elem(int row, int u, int LB) {  // element index of (row, level u) in a chunk
+  if (BYTES * LB == 64) {  // swizzled 64-byte rows
+    const int per16 = 16 / BYTES, unit = (u / per16) ^ ((row >> 1) & 3);
+    return row * LB + unit * per16 + u % per16;
+  }
+  return row * LB + u;
+}
 template <typename R, int CPT, int LB, bool CM>
 __device__ __forceinline__ Vec<R, CPT> t_ld(const Vec<R, CPT>* chunk, int u, int lane) {
   if (!CM) return chunk[u * 32 + lane];
   Vec<R, CPT> v;
   const R* e = reinterpret_cast<const R*>(chunk);
 #pragma unroll
-  for (int j = 0; j < CPT; ++j) v.v[j] = e[(j * 32 + lane) * LB + u];
+  for (int j = 0; j < CPT; ++j) v.v[j] = e[cm_elem<sizeof(R)>(j * 32 + lane, u, LB)];
   return v;
 }
 template <typename R, int CPT, int LB, bool CM>
@@ -86,7 +96,7 @@ __device__ __forceinline__ void t_st(Vec<R, CPT>* chunk, int u, int lane, const 
   }
   R* e = reinterpret_cast<R*>(chunk);
 #pragma unroll
-  for (int j = 0; j < CPT; ++j) e[(j * 32 + lane) * LB + u] = v.v[j];
+  for (int j = 0; j < CPT; ++j) e[cm_elem<sizeof(R)>(j * 32 + lane, u, LB)] = v.v[j];
 }
 
 // grid = (column tiles, matrices); block = 32 threads. Lane l owns columns c0 + l*CPT .. +CPT-1 (CM: c0 + l + 32*j).
@@ -102,7 +112,7 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
   constexpr int LB = LBT, W = 32 * CPT;
   constexpr unsigned CHUNK_BYTES = LB * W * sizeof(R);
   static_assert(LB % RN == 0, "renormalisation interval must divide the chunk");
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
   const int lane = threadIdx.x;
   const int nfull = nlev / LB, ntail = nlev - nfull * LB, nch = nfull + (ntail ? 1 : 0);
 
@@ -110,7 +120,7 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
   uint64_t* rbar = reinterpret_cast<uint64_t*>(smem_raw);
   uint64_t* pbar = rbar + NS;
   uint64_t* bbar = pbar + nch;
-  const size_t off = ((size_t)(3 * NS + nch) * 8 + 127) & ~(size_t)127;
+  const size_t off = ((size_t)(3 * NS + nch) * 8 + 1023) & ~(size_t)1023;  // chunks sit on 1 KB boundaries (swizzle atoms are 512 B)
   const size_t plane = (size_t)nch * LB * 32;  // V units
   V* P0 = reinterpret_cast<V*>(smem_raw + off);
   V* P1 = P0 + plane;
@@ -373,14 +383,14 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
 }
 
 // ------------------------------------------------------------------------------------------- host side
-// Chunk length and renormalisation interval per layout. Column-major rows are LB*sizeof(R) = 48 bytes (see t_ld).
+// Chunk length and renormalisation interval per layout. Column-major rows are 64 bytes swizzled (f64) or 48 bytes (f32), see t_ld.
 template <typename R, bool CM>
 struct TmaGeom {
   static constexpr int LB = kLB, RN = TmaCfg<R>::RN;
 };
 template <>
 struct TmaGeom<double, true> {
-  static constexpr int LB = 6, RN = 6;
+  static constexpr int LB = 8, RN = 8;  // 64-byte rows, swizzled
 };
 template <>
 struct TmaGeom<float, true> {
@@ -393,13 +403,14 @@ static int launch_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat
   constexpr int CPT = TmaCfg<R>::CPT, LB = TmaGeom<R, CM>::LB, RN = EXACT ? 1 : TmaGeom<R, CM>::RN, W = 32 * CPT;
   CUtensorMap mdl, md, mdu, mx;
   bool ok;
+  const int swz = CM && LB * sizeof(R) == 64 ? 1 : 0;
   if (CM) {  // [ncol][stride] rows of which the first nlev entries are the column: fastest dimension = level
-    ok = make_tensor_map_2d<R>(&mdl, dl, nlev, ncol, a_stride, LB, W) && make_tensor_map_2d<R>(&md, d, nlev, ncol, a_stride, LB, W) &&
-         make_tensor_map_2d<R>(&mdu, du, nlev, ncol, a_stride, LB, W) && make_tensor_map_2d<R>(&mx, X, nlev, ncol, x_stride, LB, W);
+    ok = make_tensor_map_2d<R>(&mdl, dl, nlev, ncol, a_stride, LB, W, swz) && make_tensor_map_2d<R>(&md, d, nlev, ncol, a_stride, LB, W, swz) &&
+         make_tensor_map_2d<R>(&mdu, du, nlev, ncol, a_stride, LB, W, swz) && make_tensor_map_2d<R>(&mx, X, nlev, ncol, x_stride, LB, W, swz);
   } else {
     const int64_t rows = (int64_t)nmat * nlev;
-    ok = make_tensor_map_2d<R>(&mdl, dl, ncol, rows, a_stride, W, LB) && make_tensor_map_2d<R>(&md, d, ncol, rows, a_stride, W, LB) &&
-         make_tensor_map_2d<R>(&mdu, du, ncol, rows, a_stride, W, LB) && make_tensor_map_2d<R>(&mx, X, ncol, rows, x_stride, W, LB);
+    ok = make_tensor_map_2d<R>(&mdl, dl, ncol, rows, a_stride, W, LB, 0) && make_tensor_map_2d<R>(&md, d, ncol, rows, a_stride, W, LB, 0) &&
+         make_tensor_map_2d<R>(&mdu, du, ncol, rows, a_stride, W, LB, 0) && make_tensor_map_2d<R>(&mx, X, ncol, rows, x_stride, W, LB, 0);
   }
   if (!ok) return EKAT_B200_ERR_UNSUPPORTED;
   auto k = k_tridiag_tma<R, EXACT, CPT, RN, NS, LB, CM>;
@@ -425,7 +436,7 @@ static int run_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev,
   const Tuning tu = tuning();
   const int nch = (nlev + LB - 1) / LB;
   const size_t chunk = (size_t)LB * W * sizeof(R);
-  const size_t bars = ((size_t)(12 + nch) * 8 + 127) & ~(size_t)127;
+  const size_t bars = ((size_t)(12 + nch) * 8 + 1023) & ~(size_t)1023;
   const size_t planes = (size_t)2 * nch * chunk;
   const int nrings = 2;
   // ring depth: 4 stages, or 2 if that lets one more CTA share the SM (measured: residency wins over ring depth)

@@ -10,7 +10,8 @@ namespace ekb {
 // [nrows][pitch] array of R, of which the first ncol entries of a row are data; box = boxc columns x boxr rows.
 // Columns beyond ncol / rows beyond nrows read as zero and are not written (TMA bounds handling). tridiag_tma.cu.
 template <typename R>
-bool make_tensor_map_2d(CUtensorMap* m, const R* base, int64_t ncol, int64_t nrows, int64_t pitch, int boxc, int boxr);
+bool make_tensor_map_2d(CUtensorMap* m, const R* base, int64_t ncol, int64_t nrows, int64_t pitch, int boxc, int boxr,
+                        int swizzle64 = 0);
 
 // Reciprocal for the ratio form: hardware seed (~2^-20) and one cubic Newton step (~2^-60 relative; eps is 2^-53).
 __device__ __forceinline__ double t_rcp(double x) {

@@ -540,9 +540,9 @@ static int launch_shared_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, i
                              int rh, int ns, size_t smem, cudaStream_t stream, const char* name) {
   constexpr int CPT = TmaCfg<R>::CPT, RN = EXACT ? 1 : TmaCfg<R>::RN, W = 32 * CPT;
   CUtensorMap mdl, md, mdu, mx;
-  if (!make_tensor_map_2d<R>(&mdl, dl, ncol, nlev, a_stride, W, kLB) || !make_tensor_map_2d<R>(&md, d, ncol, nlev, a_stride, W, kLB) ||
-      !make_tensor_map_2d<R>(&mdu, du, ncol, nlev, a_stride, W, kLB) ||
-      !make_tensor_map_2d<R>(&mx, X, ncol, (int64_t)nrhs * nlev, x_stride, W, kLB))
+  if (!make_tensor_map_2d<R>(&mdl, dl, ncol, nlev, a_stride, W, kLB, 0) || !make_tensor_map_2d<R>(&md, d, ncol, nlev, a_stride, W, kLB, 0) ||
+      !make_tensor_map_2d<R>(&mdu, du, ncol, nlev, a_stride, W, kLB, 0) ||
+      !make_tensor_map_2d<R>(&mx, X, ncol, (int64_t)nrhs * nlev, x_stride, W, kLB, 0))
     return EKAT_B200_ERR_UNSUPPORTED;
   auto k = k_tridiag_tma_shared<R, EXACT, CPT, RN, DBG>;
   int rc = allow_smem(k, smem);
