@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--cols-per-gpu", type=int, default=COLS_PER_GPU)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the other kernels of the path (N = 1 only)")
     return ap.parse_args()
 
 
@@ -266,6 +267,12 @@ def run_ours(args):
     if not args.no_e2e:
         e2e = run_e2e(torch, dev, comm, ncol, dl, d, du, B, x1, y1, x2, min(args.steps, 3))
 
+    extras = None
+    if size == 1 and not args.no_extras:
+        del dl, d, du, B, X, x1, y1, x2, y2
+        torch.cuda.empty_cache()
+        extras = run_extras(torch, dev, peak)
+
     if rank == 0:
         cpu = None
         if size == 1 and not args.no_cpu:
@@ -281,7 +288,7 @@ def run_ours(args):
                            "parallelism": f"column ranges over {size} rank(s), no data-path collective"},
                 "hbm_gbs": {"tridiag": tri_gbs, "lin_interp": li_gbs,
                             "step": (ALG_BYTES_TRIDIAG * NLEV + ALG_BYTES_LI * KM2) * ncol * args.steps / (ms_total * 1e-3) / 1e9},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+                "roofline": roofline, "other_kernels": extras, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
                 "verification": {"checksum_u64": hex(checksum), "residual_max": residual,
                                  "residual_ok": residual <= 50 * 2.220446049250313e-16},
                 "wall_s_timed_region": t1 - t0}
@@ -289,6 +296,66 @@ def run_ours(args):
     if size > 1:
         import torch.distributed as dist
         dist.destroy_process_group()
+
+
+def run_extras(torch, dev, peak):
+    """The other kernels of the hot path at BASELINE sizes, each timed alone with CUDA events (3 launches after 2
+    warm-ups, operands >> L2, X restored outside the events): algorithmic GB/s and fraction of the measured peak.
+    Not part of `value`; reported so that every row of SURVEY.md section 8a has a measured roofline fraction."""
+    import ekat_b200
+    from ekat_b200 import tridiag as T
+    from ekat_b200._lib import lib
+    from ekat_b200.lin_interp import LinInterp, fill as li_fill
+    out = []
+
+    def timed(fn, restore=None, reps=3):
+        for _ in range(2):
+            if restore:
+                restore()
+            fn()
+        torch.cuda.synchronize()
+        tot = 0.0
+        for _ in range(reps):
+            if restore:
+                restore()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            tot += a.elapsed_time(b)
+        return tot / reps
+
+    def tri(label, solver, ncol, nlev, nA, nrhs, layout, dt=torch.float64):
+        w = 8 if dt == torch.float64 else 4
+        dl, d, du, B = T.fill(dt, ncol, nlev, nA, nrhs, layout=layout, device=dev)
+        X = B.clone()
+        ms = timed(lambda: getattr(T, solver)(dl, d, du, X, layout=layout), restore=lambda: X.copy_(B))
+        alg = (3 * nA + 2 * nrhs) * nlev * w * ncol
+        out.append({"case": label, "kernel": lib().ekat_b200_last_kernel().decode(), "ms": ms, "gbs": alg / ms / 1e6,
+                    "frac": alg / ms / 1e6 / peak, "col_lev_per_s": ncol * nlev / ms * 1e3})
+        del dl, d, du, B, X
+        torch.cuda.empty_cache()
+
+    LM, CMJ = ekat_b200.LEV_MAJOR, ekat_b200.COL_MAJOR
+    tri("config 5 shard, bfb (bit-exact), level-major", "bfb", 3145728, 128, 1, 1, LM)
+    tri("config 4, thomas, 10 rhs sharing one matrix, level-major", "thomas", 1572864, 128, 1, 10, LM)
+    tri("config 4, bfb, 10 rhs sharing one matrix, level-major", "bfb", 1572864, 128, 1, 10, LM)
+    tri("config 3, thomas, reference (column-major) layout", "thomas", 345600, 128, 1, 1, CMJ)
+    tri("config 3, bfb, reference (column-major) layout", "bfb", 345600, 128, 1, 1, CMJ)
+    tri("config 3, thomas f32, level-major", "thomas", 345600, 128, 1, 1, LM, torch.float32)
+    tri("config 3, cr, level-major", "cr", 345600, 128, 1, 1, LM)
+    tri("config 1, thomas, 21,600 x 72 (fits L2; launch-latency bound)", "thomas", 21600, 72, 1, 1, LM)
+    for km1, N, label in ((72, 16, "config 2, LinInterp 72->128, Pack<double,16> pitch"), (72, 1, "config 2, LinInterp 72->128, scalar pitch")):
+        ncol = 345600
+        x1, y1, x2 = li_fill(torch.float64, ncol, km1, 128, N, device=dev)
+        li = LinInterp(ncol, km1, 128, torch.float64, N, device=dev)
+        y2 = torch.zeros((ncol, li.pitch2), dtype=torch.float64, device=dev)
+        ms = timed(lambda: li.run(x1, x2, y1, y2))
+        alg = (2 * km1 + 2 * 128) * 8 * ncol
+        out.append({"case": label + f" ({ncol} columns)", "kernel": lib().ekat_b200_last_kernel().decode(), "ms": ms,
+                    "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak, "col_lev_per_s": ncol * 128 / ms * 1e3})
+    return out
 
 
 def run_e2e(torch, dev, comm, ncol, dl, d, du, B, x1, y1, x2, steps):

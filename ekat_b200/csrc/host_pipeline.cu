@@ -13,16 +13,26 @@
 
 namespace ekb {
 template <typename R>
-int tridiag_levmajor(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nA, int nrhs,
-                     int64_t a_stride, int64_t x_stride, unsigned flags, cudaStream_t stream);
-template <typename R>
-int tridiag_tile(int algo, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nA, int nrhs, int64_t a_stride,
-                 int64_t x_stride, int layout, unsigned flags, cudaStream_t stream);
-template <typename R>
 int lin_interp(int mode, const R* x1, const R* x2, const R* y1, R* y2, int* indx, const int* indx_in, int64_t ncol,
                int km1, int km2, int64_t pitch1, int64_t pitch2, int nfields, int64_t y1_fstride, int64_t y2_fstride,
                cudaStream_t stream);
 }  // namespace ekb
+
+// a chunk is solved through the same entry points (and kernel selection) a caller with device views uses
+static int solve_chunk(int solver, double* dl, double* d, double* du, double* X, int64_t nc, int nlev, int nA, int nrhs,
+                       int64_t as, int64_t xs, int layout, cudaStream_t st) {
+  auto* s = reinterpret_cast<ekat_b200_stream_t>(st);
+  return solver == 2 ? ekat_b200_tridiag_cr_f64(dl, d, du, X, nc, nlev, nA, nrhs, as, xs, layout, 0, s)
+                     : solver == 1 ? ekat_b200_tridiag_bfb_f64(dl, d, du, X, nc, nlev, nA, nrhs, as, xs, layout, 0, s)
+                                   : ekat_b200_tridiag_thomas_f64(dl, d, du, X, nc, nlev, nA, nrhs, as, xs, layout, 0, s);
+}
+static int solve_chunk(int solver, float* dl, float* d, float* du, float* X, int64_t nc, int nlev, int nA, int nrhs,
+                       int64_t as, int64_t xs, int layout, cudaStream_t st) {
+  auto* s = reinterpret_cast<ekat_b200_stream_t>(st);
+  return solver == 2 ? ekat_b200_tridiag_cr_f32(dl, d, du, X, nc, nlev, nA, nrhs, as, xs, layout, 0, s)
+                     : solver == 1 ? ekat_b200_tridiag_bfb_f32(dl, d, du, X, nc, nlev, nA, nrhs, as, xs, layout, 0, s)
+                                   : ekat_b200_tridiag_thomas_f32(dl, d, du, X, nc, nlev, nA, nrhs, as, xs, layout, 0, s);
+}
 
 struct ekat_b200_pipeline {
   int nslots = 0;
@@ -82,9 +92,7 @@ int tridiag_host(ekat_b200_pipeline* p, int solver, const R* dl, const R* d, con
       if ((rc = copy2d(dd, dp, d + c0, a_stride * sizeof(R), w, rowsA, cudaMemcpyHostToDevice, st))) return rc;
       if ((rc = copy2d(ddu, dp, du + c0, a_stride * sizeof(R), w, rowsA, cudaMemcpyHostToDevice, st))) return rc;
       if ((rc = copy2d(dx, dp, X + c0, x_stride * sizeof(R), w, rowsX, cudaMemcpyHostToDevice, st))) return rc;
-      if (solver == 2) rc = tridiag_tile<R>(2, ddl, dd, ddu, dx, nc, nlev, nA, nrhs, cc, cc, layout, 0, st);
-      else rc = tridiag_levmajor<R>(solver == 1, ddl, dd, ddu, dx, nc, nlev, nA, nrhs, cc, cc, 0, st);
-      if (rc) return rc;
+      if ((rc = solve_chunk(solver, ddl, dd, ddu, dx, nc, nlev, nA, nrhs, cc, cc, layout, st))) return rc;
       if ((rc = copy2d(X + c0, x_stride * sizeof(R), dx, dp, w, rowsX, cudaMemcpyDeviceToHost, st))) return rc;
     } else {
       // device chunk: [col][lev][p], tightly packed
@@ -95,9 +103,7 @@ int tridiag_host(ekat_b200_pipeline* p, int solver, const R* dl, const R* d, con
       if ((rc = copy2d(dd, wa, d + c0 * a_stride, a_stride * sizeof(R), wa, nc, cudaMemcpyHostToDevice, st))) return rc;
       if ((rc = copy2d(ddu, wa, du + c0 * a_stride, a_stride * sizeof(R), wa, nc, cudaMemcpyHostToDevice, st))) return rc;
       if ((rc = copy2d(dx, wx, X + c0 * x_stride, x_stride * sizeof(R), wx, nc, cudaMemcpyHostToDevice, st))) return rc;
-      rc = tridiag_tile<R>(solver == 2 ? 2 : (solver == 1 ? 1 : 0), ddl, dd, ddu, dx, nc, nlev, nA, nrhs, ea, ex, layout,
-                           0, st);
-      if (rc) return rc;
+      if ((rc = solve_chunk(solver, ddl, dd, ddu, dx, nc, nlev, nA, nrhs, ea, ex, layout, st))) return rc;
       if ((rc = copy2d(X + c0 * x_stride, x_stride * sizeof(R), dx, wx, wx, nc, cudaMemcpyDeviceToHost, st))) return rc;
     }
     p->h2d += (uint64_t)nc * per_col;

@@ -39,6 +39,18 @@ for c in cases:
             for _ in range(REPS):
                 X.copy_(B)
                 getattr(T, s)(dl, d, du, X, layout=ekat_b200.COL_MAJOR)
+    elif c in ("shared_thomas", "shared_bfb"):
+        dl, d, du, B = T.fill(dt, NCOL, NLEV, 1, 10, device=dev)
+        X = B.clone()
+        for _ in range(REPS):
+            X.copy_(B)
+            getattr(T, c.split("_")[1])(dl, d, du, X)
+    elif c in ("col_thomas", "col_bfb"):
+        dl, d, du, B = T.fill(dt, NCOL, NLEV, 1, 1, layout=ekat_b200.COL_MAJOR, device=dev)
+        X = B.clone()
+        for _ in range(REPS):
+            X.copy_(B)
+            getattr(T, c.split("_")[1])(dl, d, du, X, layout=ekat_b200.COL_MAJOR)
     elif c == "li":
         for km1 in (72, 128):
             x1, y1, x2 = li_fill(dt, NCOL, km1, 128, 1, device=dev)
