@@ -325,12 +325,19 @@ template <typename R>
 int tridiag_levmajor(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nA, int nrhs,
                      int64_t a_stride, int64_t x_stride, unsigned flags, cudaStream_t stream) {
   const bool clobber = (flags & EKAT_B200_CLOBBER_DIAGS) != 0;
-  if (nA == nrhs && !clobber && tuning().variant == 0) {
-    const int rc = tridiag_tma<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
+  const int variant = tuning().variant;
+  // One matrix per column (shared by all its right-hand sides): the persistent warp-specialised kernel. With a single
+  // right-hand side it is used for thomas (factor and solve chains on different warps: 90% of the HBM peak against 77%
+  // for the one-warp kernel); bfb with a single right-hand side is bound by its division chain on either kernel and
+  // keeps the one-warp kernel, which holds three tiles per SM instead of two (measured: 54% against 47%); so does f32
+  // thomas (72% against 63%: half the bytes per level for the same number of barrier hand-offs).
+  const bool split_ok = nA == 1 && !clobber && (variant == 0 || variant == 7 || variant == 8 || variant == 9);
+  if (split_ok && (nrhs > 1 || (!exact && sizeof(R) == 8) || variant == 7 || variant == 9)) {
+    const int rc = tridiag_tma_shared<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }
-  if (nA == 1 && nrhs > 1 && !clobber && (tuning().variant == 0 || tuning().variant == 7 || tuning().variant == 8)) {
-    const int rc = tridiag_tma_shared<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
+  if (nA == nrhs && !clobber && (variant == 0 || variant == 4)) {
+    const int rc = tridiag_tma<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }
   constexpr int VEC = 16 / sizeof(R);

@@ -138,6 +138,13 @@ if __name__ == "__main__":
             tridiag_case(s, "f32", 345600, 128)
             tridiag_case(s, "f64", 3145728, 128)
             tridiag_case(s, "f64", 21600, 72)
+    if "split" in what:  # one right-hand side: warp-specialised kernel (default for thomas) against the one-warp kernel (variant 4)
+        for s in ("bfb", "thomas"):
+            for dt in ("f64", "f32"):
+                tridiag_case(s, dt, 345600, 128, tunings=[(0, 0, 0), (0, 0, 4), (0, 0, 9)])
+            tridiag_case(s, "f64", 3145728, 128, tunings=[(0, 0, 0), (0, 0, 4), (0, 0, 9)])
+            tridiag_case(s, "f64", 21600, 72, tunings=[(0, 0, 0), (0, 0, 4), (0, 0, 9)])
+            tridiag_case(s, "f64", 345600, 72, tunings=[(0, 0, 0), (0, 0, 4), (0, 0, 9)])
     if "c1" in what:
         for s in ("thomas", "bfb", "cr"):
             tridiag_case(s, "f64", 21600, 72, tunings=[(0, 0, 0), (16, 8, 0), (16, 16, 0), (32, 8, 0), (64, 16, 0)])
