@@ -84,7 +84,7 @@ static int tridiag_entry(int solver, R* dl, R* d, R* du, R* X, int64_t ncol, int
   if (solver == SOLVER_CR) return tridiag_tile<R>(2, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, layout, flags, st);
   if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && tuning().variant != 2)
     return tridiag_levmajor<R>(solver == SOLVER_BFB, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, flags, st);
-  if (layout == EKAT_B200_LAYOUT_COL_MAJOR && nA == 1 && nrhs == 1 && !flags && tuning().variant == 0) {
+  if (layout == EKAT_B200_LAYOUT_COL_MAJOR && nA == 1 && nrhs == 1 && !flags && (tuning().variant == 0 || tuning().variant == 4)) {
     // reference layout, one right-hand side: the TMA kernel reads the columns where they lie (tridiag_tma.cu)
     const int rc = tridiag_tma_cm<R>(solver == SOLVER_BFB, dl, d, du, X, ncol, nlev, a_stride, x_stride, st);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;

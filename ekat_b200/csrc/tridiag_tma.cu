@@ -382,6 +382,226 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
   if (lane == 0) tma_store_wait_read<0>();  // shared memory must outlive the stores' reads
 }
 
+// ------------------------------------------------------------------------------------------- bfb, x' kept in L2
+// bfb is bound by its division chain per level (ncu: the one warp of a tile is either issuing or waiting on a
+// fixed-latency dependency 72% of the time), so its throughput is the number of tiles an SM can hold. This kernel
+// keeps only the pivots d' of a tile in shared memory; the forward sweep writes x' back IN PLACE over X -- exactly
+// what the reference's sweep does (ekat_tridiag.hpp:305-320) -- with an evict-last hint, and the back-substitution
+// reads it (and du, as before) again through the ring. A tile's x' (32 KB) is re-read ~20 us after it was written
+// and overwritten by the solution right after, so it lives and dies in the 126 MB L2: HBM still sees one read of
+// dl, d, du, X and one write of X. Shared memory per tile drops from 72 KB to ~51 KB: four tiles per SM instead of
+// three. The top chunk is never spilled: the back-substitution starts from it where it lies.
+// Ring stage = [dl | du | x], LB levels each. Use u < nch: forward chunk u. Use u >= nch: (du, x') of chunk
+// 2*nch-2-u for the back-substitution. A stage is refilled once the tensor store that reads it has done so.
+template <typename R, int CPT, int NS, int LBT, bool CM>
+__global__ void __launch_bounds__(32)
+k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
+                    const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mx, R* __restrict__ X,
+                    int64_t ncol, int nlev, int64_t x_stride, int pd) {
+  using V = Vec<R, CPT>;
+  constexpr int LB = LBT, W = 32 * CPT, CH = LB * 32;
+  constexpr unsigned CHUNK_BYTES = LB * W * sizeof(R);
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  const int lane = threadIdx.x;
+  const int nfull = nlev / LB, ntail = nlev - nfull * LB, nch = nfull + (ntail ? 1 : 0);
+  const int NU = 2 * nch - 1;  // ring uses
+
+  uint64_t* rbar = reinterpret_cast<uint64_t*>(smem_raw);  // [NS] ring stage landed
+  uint64_t* pbar = rbar + NS;                              // [nch] pivot-plane chunk landed
+  constexpr size_t AL = CM ? 1024 : 128;  // swizzled chunks sit on 1 KB boundaries
+  const size_t off = ((size_t)(NS + nch) * 8 + AL - 1) & ~(AL - 1);
+  V* P0 = reinterpret_cast<V*>(smem_raw + off);  // d -> d'
+  V* RG = P0 + (size_t)nch * CH;                 // [NS][3][LB][32]
+
+  const int c0 = blockIdx.x * W;
+  const int row0 = blockIdx.y * nlev;
+  if (lane == 0) {
+    for (int s = 0; s < NS + nch; ++s) mbar_init(&rbar[s], 1);
+    fence_mbar_init();
+  }
+  __syncwarp();
+  const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
+
+  auto load_chunk = [&](void* dst, const CUtensorMap* m, int k, uint64_t* bar, uint64_t pol) {
+    if (CM) tma_load_2d_hint(dst, m, k * LB, c0, bar, pol);
+    else tma_load_2d_hint(dst, m, c0, row0 + k * LB, bar, pol);
+  };
+  auto store_chunk = [&](int k, const void* src, uint64_t pol) {
+    if (CM) tma_store_2d_hint(&mx, k * LB, c0, src, pol);
+    else tma_store_2d_hint(&mx, c0, row0 + k * LB, src, pol);
+    tma_store_commit();
+  };
+  auto issue_use = [&](int u) {
+    const int s = u % NS;
+    V* st = RG + (size_t)s * 3 * CH;
+    if (u < nch) {
+      mbar_expect_tx(&rbar[s], 3u * CHUNK_BYTES);
+      load_chunk(st, &mdl, u, &rbar[s], pol_stream);
+      load_chunk(st + CH, &mdu, u, &rbar[s], pol_keep);  // read again by the back-substitution
+      load_chunk(st + 2 * CH, &mx, u, &rbar[s], pol_stream);
+    } else {
+      const int k = 2 * nch - 2 - u;
+      mbar_expect_tx(&rbar[s], 2u * CHUNK_BYTES);
+      load_chunk(st + CH, &mdu, k, &rbar[s], pol_stream);
+      load_chunk(st + 2 * CH, &mx, k, &rbar[s], pol_stream);  // x', written by this CTA during the forward sweep
+    }
+  };
+  auto issue_plane = [&](int k) {
+    mbar_expect_tx(&pbar[k], CHUNK_BYTES);
+    load_chunk(P0 + (size_t)k * CH, &md, k, &pbar[k], pol_stream);
+  };
+  auto ld = [&](const V* chunk, int u) { return t_ld<R, CPT, LB, CM>(chunk, u, lane); };
+  if (lane == 0) {
+    for (int k = 0; k < pd && k < nch; ++k) issue_plane(k);
+    for (int u = 0; u < NS && u < nch; ++u) issue_use(u);
+  }
+
+  // ---------------------------------------------------------------- forward sweep
+  R dprev[CPT], xprev[CPT], uprev[CPT];
+#pragma unroll
+  for (int j = 0; j < CPT; ++j) {
+    dprev[j] = (R)1;
+    xprev[j] = (R)0;
+    uprev[j] = (R)0;
+  }
+  for (int k = 0; k < nch; ++k) {
+    const int s = k % NS;
+    mbar_wait(&rbar[s], (unsigned)(k / NS) & 1u);
+    mbar_wait(&pbar[k], 0u);
+    V* st = RG + (size_t)s * 3 * CH;
+    V* p0 = P0 + (size_t)k * CH;
+    V a[LB], b[LB], c[LB], x[LB], o0[LB], o1[LB];
+#pragma unroll
+    for (int u = 0; u < LB; ++u) {
+      a[u] = ld(st, u);
+      c[u] = ld(st + CH, u);
+      x[u] = ld(st + 2 * CH, u);
+      b[u] = ld(p0, u);
+    }
+    R sd[CPT], sx[CPT], su[CPT];
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      sd[j] = dprev[j];
+      sx[j] = xprev[j];
+      su[j] = uprev[j];
+    }
+    bool bad = false;
+    bfb_fwd_chunk<R, CPT, LB, false>(a, b, c, x, o0, o1, dprev, xprev, uprev, k == 0, bad);
+    if (__any_sync(0xffffffffu, bad)) {  // rare operands somewhere in the warp: redo with the full-range division
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) {
+        dprev[j] = sd[j];
+        xprev[j] = sx[j];
+        uprev[j] = su[j];
+      }
+      bfb_fwd_chunk<R, CPT, LB, true>(a, b, c, x, o0, o1, dprev, xprev, uprev, k == 0, bad);
+    }
+#pragma unroll
+    for (int u = 0; u < LB; ++u) {
+      t_st<R, CPT, LB, CM>(p0, u, lane, o0[u]);
+      t_st<R, CPT, LB, CM>(st + 2 * CH, u, lane, o1[u]);
+    }
+    const bool spill = k < nch - 1;  // the top chunk stays where it is
+    if (spill) fence_proxy_async();
+    __syncwarp();
+    if (lane == 0) {
+      if (spill) store_chunk(k, st + 2 * CH, pol_keep);
+      if (k >= 1 && k - 1 + NS < nch) {  // the stage of chunk k-1 is free once its store has read it
+        if (spill) tma_store_wait_read<1>();
+        else tma_store_wait_read<0>();
+        issue_use(k - 1 + NS);
+      }
+      if (k + pd < nch) issue_plane(k + pd);
+    }
+  }
+  // turn-around: every x' must have reached L2 before it is read back
+  if (lane == 0) {
+    tma_store_wait_all<0>();
+    for (int u = nch; u < NU && u < nch + NS - 1; ++u) issue_use(u);
+  }
+
+  // ---------------------------------------------------------------- back substitution
+  R xv[CPT];
+#pragma unroll
+  for (int j = 0; j < CPT; ++j) xv[j] = (R)0;
+  for (int jb = 0; jb < nch; ++jb) {
+    const int k = nch - 1 - jb, u0 = nch - 1 + jb, s = u0 % NS;
+    if (jb > 0) mbar_wait(&rbar[s], (unsigned)(u0 / NS) & 1u);
+    V* st = RG + (size_t)s * 3 * CH;
+    const V* bu = st + CH;
+    V* xs = st + 2 * CH;
+    const V* q0p = P0 + (size_t)k * CH;
+    bool stored = true;
+    if (k == nfull) {
+      // partial top chunk (ntail levels)
+      const int64_t col = (int64_t)c0 + lane * CPT;
+      for (int u = ntail - 1; u >= 0; --u) {
+        const V y = ld(xs, u), m0 = ld(q0p, u);
+        V ui = ld(bu, u), o;
+        if (u == ntail - 1) {  // du(nrow-1) is never used (:24-27)
+#pragma unroll
+          for (int j = 0; j < CPT; ++j) ui.v[j] = (R)0;
+        }
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) {
+          xv[j] = x_div(x_sub(y.v[j], x_mul(ui.v[j], xv[j])), m0.v[j]);  // :317-319
+          o.v[j] = xv[j];
+        }
+        if (CM) {
+          t_st<R, CPT, LB, CM>(xs, u, lane, o);
+        } else {  // a tensor store would spill into the next matrix' rows -> plain streaming stores
+          R* g = X + (size_t)(row0 + k * LB + u) * x_stride + col;
+#pragma unroll
+          for (int j = 0; j < CPT; ++j)
+            if (col + j < ncol) __stcs(g + j, o.v[j]);
+        }
+      }
+      if (CM) fence_proxy_async();
+      else stored = false;
+    } else {
+      V y[LB], m0[LB], ui[LB];
+#pragma unroll
+      for (int u = 0; u < LB; ++u) {
+        y[u] = ld(xs, u);
+        m0[u] = ld(q0p, u);
+        ui[u] = ld(bu, u);
+      }
+      if (jb == 0) {  // this chunk ends with the last level
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) ui[LB - 1].v[j] = (R)0;
+      }
+      R sxv[CPT];
+      V ys[LB];
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) sxv[j] = xv[j];
+#pragma unroll
+      for (int u = 0; u < LB; ++u) ys[u] = y[u];
+      bool bad = false;
+      bfb_bwd_chunk<R, CPT, LB, false>(y, m0, ui, xv, bad);
+      if (__any_sync(0xffffffffu, bad)) {
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) xv[j] = sxv[j];
+#pragma unroll
+        for (int u = 0; u < LB; ++u) y[u] = ys[u];
+        bfb_bwd_chunk<R, CPT, LB, true>(y, m0, ui, xv, bad);
+      }
+#pragma unroll
+      for (int u = 0; u < LB; ++u) t_st<R, CPT, LB, CM>(xs, u, lane, y[u]);
+      fence_proxy_async();  // generic-proxy writes of this chunk -> visible to the TMA store
+    }
+    __syncwarp();
+    if (lane == 0) {
+      if (stored) store_chunk(k, xs, pol_stream);
+      if (jb >= 1 && u0 - 1 + NS < NU) {  // the stage of the previous step is free once its store has read it
+        if (stored) tma_store_wait_read<1>();
+        else tma_store_wait_read<0>();
+        issue_use(u0 - 1 + NS);
+      }
+    }
+  }
+  if (lane == 0) tma_store_wait_read<0>();  // shared memory must outlive the stores' reads
+}
+
 // ------------------------------------------------------------------------------------------- host side
 // Chunk length and renormalisation interval per layout. Column-major rows are 64 bytes swizzled (f64) or 48 bytes (f32), see t_ld.
 template <typename R, bool CM>
@@ -422,6 +642,31 @@ static int launch_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat
   return check_cuda(cudaGetLastError());
 }
 
+template <typename R, int NS, bool CM>
+static int launch_spill(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
+                        int pd, size_t smem, cudaStream_t stream, const char* name) {
+  constexpr int CPT = TmaCfg<R>::CPT, LB = TmaGeom<R, CM>::LB, W = 32 * CPT;
+  CUtensorMap mdl, md, mdu, mx;
+  bool ok;
+  const int swz = CM && LB * sizeof(R) == 64 ? 1 : 0;
+  if (CM) {
+    ok = make_tensor_map_2d<R>(&mdl, dl, nlev, ncol, a_stride, LB, W, swz) && make_tensor_map_2d<R>(&md, d, nlev, ncol, a_stride, LB, W, swz) &&
+         make_tensor_map_2d<R>(&mdu, du, nlev, ncol, a_stride, LB, W, swz) && make_tensor_map_2d<R>(&mx, X, nlev, ncol, x_stride, LB, W, swz);
+  } else {
+    const int64_t rows = (int64_t)nmat * nlev;
+    ok = make_tensor_map_2d<R>(&mdl, dl, ncol, rows, a_stride, W, LB, 0) && make_tensor_map_2d<R>(&md, d, ncol, rows, a_stride, W, LB, 0) &&
+         make_tensor_map_2d<R>(&mdu, du, ncol, rows, a_stride, W, LB, 0) && make_tensor_map_2d<R>(&mx, X, ncol, rows, x_stride, W, LB, 0);
+  }
+  if (!ok) return EKAT_B200_ERR_UNSUPPORTED;
+  auto k = k_tridiag_bfb_spill<R, CPT, NS, LB, CM>;
+  int rc = allow_smem(k, smem);
+  if (rc) return rc;
+  dim3 grid((unsigned)((ncol + W - 1) / W), (unsigned)nmat);
+  k<<<grid, 32, smem, stream>>>(mdl, md, mdu, mx, X, ncol, nlev, x_stride, pd);
+  note_launch(name);
+  return check_cuda(cudaGetLastError());
+}
+
 // Returns EKAT_B200_ERR_UNSUPPORTED when the operands do not meet TMA's requirements (16-byte aligned bases and
 // pitches, column fits on chip, sizes within tensor-map limits); the caller then uses the cp.async / tile kernels.
 template <typename R, bool CM>
@@ -436,6 +681,29 @@ static int run_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev,
   const Tuning tu = tuning();
   const int nch = (nlev + LB - 1) / LB;
   const size_t chunk = (size_t)LB * W * sizeof(R);
+  const bool f64 = sizeof(R) == 8;
+  if (exact && tu.variant != 4) {
+    // bfb: pivots on chip, x' through L2 (k_tridiag_bfb_spill): as many tiles per SM as a 3- or 4-stage ring allows
+    const size_t al = CM ? 1024 : 128;
+    auto smem_for = [&](int stages) {
+      return (((size_t)(stages + nch) * 8 + al - 1) & ~(al - 1)) + (size_t)nch * chunk + (size_t)stages * 3 * chunk;
+    };
+    auto tiles = [&](int stages) { return (int)((kMaxSmemPerCta + 1024) / (smem_for(stages) + 1024)); };
+    // three stages (two chunks in flight behind the one being swept) are what the re-loads of the back-substitution
+    // need; a fourth only if it costs no residency; two only if nothing else fits (measured: 2 stages 49-51%,
+    // 3 stages 57-62%, 4 stages at one tile fewer 46%)
+    int ns = tiles(4) == tiles(3) ? 4 : 3;
+    if (smem_for(ns) > kMaxSmemPerCta) ns = 2;
+    if (tu.cols_per_cta >= 2 && tu.cols_per_cta <= 4) ns = tu.cols_per_cta;
+    if (smem_for(ns) <= kMaxSmemPerCta) {
+      const int pd = tu.prefetch > 0 ? tu.prefetch : 3;
+      const char* name = CM ? (f64 ? "tridiag_bfb_spill_cm<f64>" : "tridiag_bfb_spill_cm<f32>")
+                            : (f64 ? "tridiag_bfb_spill<f64>" : "tridiag_bfb_spill<f32>");
+      return ns == 4   ? launch_spill<R, 4, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem_for(4), stream, name)
+             : ns == 3 ? launch_spill<R, 3, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem_for(3), stream, name)
+                       : launch_spill<R, 2, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem_for(2), stream, name);
+    }
+  }
   const size_t bars = ((size_t)(12 + nch) * 8 + 1023) & ~(size_t)1023;
   const size_t planes = (size_t)2 * nch * chunk;
   const int nrings = 2;
@@ -447,7 +715,6 @@ static int run_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev,
   if (smem > kMaxSmemPerCta) return EKAT_B200_ERR_UNSUPPORTED;
   int pd = tu.prefetch > 0 ? tu.prefetch : (CM ? 4 : 3);  // plane chunks in flight ahead of the sweep
   if (pd < 1) pd = 1;
-  const bool f64 = sizeof(R) == 8;
   const char* name = CM ? (exact ? (f64 ? "tridiag_tma_cm<f64,bfb>" : "tridiag_tma_cm<f32,bfb>")
                                  : (f64 ? "tridiag_tma_cm<f64,thomas>" : "tridiag_tma_cm<f32,thomas>"))
                         : (exact ? (f64 ? "tridiag_tma<f64,bfb>" : "tridiag_tma<f32,bfb>")

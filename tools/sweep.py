@@ -145,6 +145,13 @@ if __name__ == "__main__":
             tridiag_case(s, "f64", 3145728, 128, tunings=[(0, 0, 0), (0, 0, 4), (0, 0, 9)])
             tridiag_case(s, "f64", 21600, 72, tunings=[(0, 0, 0), (0, 0, 4), (0, 0, 9)])
             tridiag_case(s, "f64", 345600, 72, tunings=[(0, 0, 0), (0, 0, 4), (0, 0, 9)])
+    if "bfb" in what:
+        for dt in ("f64", "f32"):
+            tridiag_case("bfb", dt, 345600, 128, tunings=[(0, 0, 0), (2, 0, 0), (3, 0, 0), (4, 0, 0), (2, 1, 0), (2, 5, 0), (0, 0, 4)])
+        tridiag_case("bfb", "f64", 3145728, 128, tunings=[(0, 0, 0), (2, 0, 0), (3, 0, 0), (0, 0, 4)])
+        tridiag_case("bfb", "f64", 345600, 72, tunings=[(0, 0, 0), (2, 0, 0), (3, 0, 0), (4, 0, 0)])
+        tridiag_case("bfb", "f64", 345600, 128, layout=ekat_b200.COL_MAJOR, tunings=[(0, 0, 0), (2, 0, 0), (3, 0, 0), (0, 0, 4)])
+        tridiag_case("bfb", "f64", 345600, 128, 10, 10)
     if "c1" in what:
         for s in ("thomas", "bfb", "cr"):
             tridiag_case(s, "f64", 21600, 72, tunings=[(0, 0, 0), (16, 8, 0), (16, 16, 0), (32, 8, 0), (64, 16, 0)])
