@@ -19,6 +19,9 @@ template <typename R>
 int tridiag_tma_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride,
                    cudaStream_t stream);
 template <typename R>
+int tridiag_tma_shared_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride,
+                          cudaStream_t stream);
+template <typename R>
 int lin_interp(int mode, const R* x1, const R* x2, const R* y1, R* y2, int* indx, const int* indx_in, int64_t ncol,
                int km1, int km2, int64_t pitch1, int64_t pitch2, int nfields, int64_t y1_fstride, int64_t y2_fstride,
                cudaStream_t stream);
@@ -86,6 +89,10 @@ static int tridiag_entry(int solver, R* dl, R* d, R* du, R* X, int64_t ncol, int
     return tridiag_levmajor<R>(solver == SOLVER_BFB, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, flags, st);
   if (layout == EKAT_B200_LAYOUT_COL_MAJOR && nA == 1 && nrhs == 1 && !flags && (tuning().variant == 0 || tuning().variant == 4)) {
     // reference layout, one right-hand side: the TMA kernel reads the columns where they lie (tridiag_tma.cu)
+    if (solver == SOLVER_THOMAS && tuning().variant == 0) {  // f64: factor and solve chains on different warps
+      const int rc = tridiag_tma_shared_cm<R>(false, dl, d, du, X, ncol, nlev, a_stride, x_stride, st);
+      if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+    }
     const int rc = tridiag_tma_cm<R>(solver == SOLVER_BFB, dl, d, du, X, ncol, nlev, a_stride, x_stride, st);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }

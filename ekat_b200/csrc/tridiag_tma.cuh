@@ -45,6 +45,42 @@ constexpr int kLB = 8;  // levels per TMA box / mbarrier phase / unrolled chunk
 // bfb sweeps over one chunk of LB levels held in registers. SLOW = false: speculative IEEE division (div_spec: no
 // branch on the dependent chain, out-of-range operands only raise `bad`); SLOW = true: the compiler's full-range
 // division. The kernel runs the speculative form and repeats the chunk in SLOW form if any lane raised the flag.
+// Element (level u of a chunk, lane, j-th column of the lane) of a shared-memory chunk of LB levels x W columns.
+//   level-major operands (CM = false): the TMA box is LB rows of W columns -> [u][lane][j], one vector access;
+//   the reference's column-major operands (CM = true: a column's levels are contiguous in memory,
+//   tests/algorithm/tridiag_tests_performance.cpp:181-185): the box is W rows (columns) of LB levels -> [j*32+lane][u].
+//   A level step of the warp then strides by the row length, which TMA wants in multiples of 16 bytes -- never an
+//   odd number of words, so some bank conflict is the price of needing no transpose pass. Rows of 64 bytes with the
+//   TMA's 64-byte swizzle (16-byte unit index XOR bits 7-8 of the address, i.e. XOR (row/2)%4) spread a level over
+//   8 of the 16 bank pairs (f64: 4 wavefronts instead of 2); unswizzled 48-byte rows do the same for f32.
+template <int BYTES>
+__device__ __forceinline__ int cm_elem(int row, int u, int LB) {  // element index of (row, level u) in a chunk
+  if (BYTES * LB == 64) {  // swizzled 64-byte rows
+    const int per16 = 16 / BYTES, unit = (u / per16) ^ ((row >> 1) & 3);
+    return row * LB + unit * per16 + u % per16;
+  }
+  return row * LB + u;
+}
+template <typename R, int CPT, int LB, bool CM>
+__device__ __forceinline__ Vec<R, CPT> t_ld(const Vec<R, CPT>* chunk, int u, int lane) {
+  if (!CM) return chunk[u * 32 + lane];
+  Vec<R, CPT> v;
+  const R* e = reinterpret_cast<const R*>(chunk);
+#pragma unroll
+  for (int j = 0; j < CPT; ++j) v.v[j] = e[cm_elem<sizeof(R)>(j * 32 + lane, u, LB)];
+  return v;
+}
+template <typename R, int CPT, int LB, bool CM>
+__device__ __forceinline__ void t_st(Vec<R, CPT>* chunk, int u, int lane, const Vec<R, CPT>& v) {
+  if (!CM) {
+    chunk[u * 32 + lane] = v;
+    return;
+  }
+  R* e = reinterpret_cast<R*>(chunk);
+#pragma unroll
+  for (int j = 0; j < CPT; ++j) e[cm_elem<sizeof(R)>(j * 32 + lane, u, LB)] = v.v[j];
+}
+
 template <typename R, int CPT, int LB, bool SLOW>
 __device__ __forceinline__ void bfb_fwd_chunk(const Vec<R, CPT> (&a)[LB], const Vec<R, CPT> (&b)[LB], const Vec<R, CPT> (&c)[LB],
                                               const Vec<R, CPT> (&x)[LB], Vec<R, CPT> (&o0)[LB], Vec<R, CPT> (&o1)[LB],

@@ -1,32 +1,38 @@
-// tridiag_tma_shared.cu -- batched Thomas / bfb, ONE matrix shared by many right-hand sides (nA == 1, nrhs > 1),
-// native level-major layout, TMA-fed, persistent warp-specialised CTAs.
+// tridiag_tma_shared.cu -- batched Thomas / bfb with ONE matrix per column shared by all its right-hand sides
+// (nA == 1; nrhs >= 1), TMA-fed, persistent warp-specialised CTAs. Native level-major operands; with one
+// right-hand side also the reference's column-major operands (CM).
 //
 // Replaces the per-column loops around ekat::tridiag::thomas(team, dl, d, du, X[nrow][nrhs])
 // (reference src/algorithm/ekat_tridiag.hpp:177-214, :323-334: factorize once in Kokkos::single, barrier, one
 // solve per right-hand side) and ekat::tridiag::bfb with rank-1 A (:292-320, :632-648) -- BASELINE config 4
-// (10 tracers diffused by one SHOC-style matrix per column).
+// (10 tracers diffused by one SHOC-style matrix per column) and, with nrhs == 1, the thomas of configs 1, 3, 5.
 //
 // Why this shape. Per column-level the kernel moves 3 + 2*nrhs words and does ~5*nrhs flops, so it is HBM-bound
 // as long as the forward sweep's intermediates never leave the chip: a tile of 32 columns x 128 levels needs one
 // plane (32 KB, f64) per right-hand side plus one for the factor, i.e. five right-hand sides fill an SM. With one
-// CTA per SM nothing hides a tile's load latency unless the CTA itself overlaps tiles, hence:
+// or two CTAs per SM nothing hides a tile's load latency unless the CTA itself overlaps tiles, hence:
 //  * persistent CTAs walk work items (column tile, group of rh right-hand sides);
 //  * warp roles: rh solver warps (one right-hand side each, lane = column), one factor warp, two producer warps
-//    (one elected lane each) that only issue TMA copies -- every wait in the kernel is an mbarrier wait;
+//    (one elected lane each) that only issue TMA copies, and -- block size permitting -- one io warp per solver
+//    warp that issues its tensor stores and refills (a TMA issue costs the issuing thread ~130 cycles);
+//    every wait in the kernel is an mbarrier wait;
 //  * the factor warp turns (dl, d) into (m, r) [thomas] or (dl) into (m) [bfb] in place in a ring stage that the
 //    TMA filled and hands it to the solver warps through a second mbarrier; du becomes c' = du*r [thomas] / d
-//    becomes the pivots d' [bfb] in place in a plane that stays until back-substitution;
+//    becomes the pivots d' [bfb] in place in a plane that stays until back-substitution. With factor and solve
+//    chains on different warps a single right-hand side already runs at 90% of the HBM peak (thomas, f64);
 //  * every solver warp keeps its right-hand side in a plane: B lands there by TMA, the forward sweep overwrites it
 //    with y*r [thomas] / x' [bfb], the back-substitution overwrites it with the solution, which leaves by TMA
-//    tensor stores 8 levels at a time. As soon as a chunk's store has been read out, the same lane issues the
-//    load of the NEXT work item's chunk into it; chunk 0 -- freed last, needed first -- alternates between two
-//    "head" slots so that it is loaded a whole item ahead;
+//    tensor stores 8 levels at a time. As soon as a chunk's store has been read out, the load of the NEXT work
+//    item's chunk goes into the same slot; the slot order is mirrored from one item to the next (see below), so
+//    that every chunk is requested a whole sweep before it is needed;
 //  * thomas: the factor warp runs the continuant ("ratio") recurrence (no division on its dependent chain, see
 //    tridiag_tma.cu); solver warps have one FMA per level on their chains in both sweeps.
 //  * bfb: the reference's operation order with separately rounded * - / (bit-identical); du for the
-//    back-substitution is read again from L2 through the ring instead of occupying a plane.
-// HBM traffic is the algorithmic minimum when all right-hand sides fit one CTA; otherwise the nrhs/rh groups of a
-// tile run on neighbouring CTAs at the same time and share dl, d, du through L2.
+//    back-substitution is read again from L2 through the ring instead of occupying a plane, and the ring's other
+//    half carries the refined reciprocals of the pivots, computed once by the factor warp for all solver warps.
+// HBM traffic is the algorithmic minimum (ncu: 8.09 GB moved for 8.14 GB algorithmic at 345,600 x 128 x 10); when
+// the right-hand sides do not fit one CTA, the nrhs/rh groups of a tile run on neighbouring CTAs at the same time
+// and share dl, d, du through L2. The hand-off protocol is checked by tools/sim_shared_protocol.py.
 #include "tridiag_tma.cuh"
 
 namespace ekb {
@@ -74,7 +80,7 @@ __device__ __forceinline__ void trace_put(int it, int idx, long long v) {
 //   Chunk k of a plane lives in slot k for even work items and in slot nch-1-k for odd ones: the back-substitution
 //   frees slots top chunk first, which is exactly the order in which the next item's forward sweep needs them, so
 //   every chunk of the next item is requested a whole sweep before it is used and no slot is double-buffered.
-template <typename R, bool EXACT, int CPT, int RN, bool DBG>
+template <typename R, bool EXACT, int CPT, int RN, bool DBG, bool CM>
 __global__ void __launch_bounds__(512, 1)
 k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
                      const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mx, R* __restrict__ X,
@@ -83,7 +89,7 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
   constexpr int LB = kLB, W = 32 * CPT, CH = LB * 32;
   constexpr unsigned CHUNK_BYTES = LB * W * sizeof(R);
   static_assert(LB % RN == 0, "renormalisation interval must divide the chunk");
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nfull = nlev / LB, ntail = nlev - nfull * LB, nch = nfull + (ntail ? 1 : 0), nslot = nch;
   const int UPT = EXACT ? 2 * nch : nch;  // ring uses per work item
@@ -95,7 +101,8 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
   uint64_t* cfree = plc + nslot;                          // [nslot] all solver warps have read the slot (back-substitution)
   uint64_t* plx = cfree + nslot;                          // [rh][nslot] TMA landed in a right-hand-side slot
   uint64_t* xdone = plx + rh * nslot;                     // [rh][nslot] solver warp finished a slot: solution ready to be stored
-  const size_t off = ((size_t)(3 * NS + (2 + 2 * rh) * nslot) * 8 + 127) & ~(size_t)127;
+  constexpr size_t AL = CM ? 1024 : 128;  // column-major chunks are swizzled: they sit on 1 KB boundaries (see t_ld)
+  const size_t off = ((size_t)(3 * NS + (2 + 2 * rh) * nslot) * 8 + AL - 1) & ~(AL - 1);
   V* PC = reinterpret_cast<V*>(smem_raw + off);
   V* PX = PC + (size_t)nslot * CH;
   V* RING = PX + (size_t)rh * nslot * CH;
@@ -131,6 +138,22 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
     }
   };
   const uint64_t pol_stream = l2_policy_evict_first();
+  // CM: the reference's column-major operands (one right-hand side): boxes are 32 columns x LB levels, coordinates
+  // (level, column) instead of (column, level); element access through t_ld / t_st (tridiag_tma.cuh)
+  auto ld = [&](const V* chunk, int u) { return t_ld<R, CPT, LB, CM>(chunk, u, lane); };
+  auto stv = [&](V* chunk, int u, const V& v) { t_st<R, CPT, LB, CM>(chunk, u, lane, v); };
+  auto tload = [&](void* dst, const CUtensorMap* m, int col, int row, uint64_t* bar) {
+    if (CM) tma_load_2d(dst, m, row, col, bar);
+    else tma_load_2d(dst, m, col, row, bar);
+  };
+  auto tload_hint = [&](void* dst, const CUtensorMap* m, int col, int row, uint64_t* bar, uint64_t pol) {
+    if (CM) tma_load_2d_hint(dst, m, row, col, bar, pol);
+    else tma_load_2d_hint(dst, m, col, row, bar, pol);
+  };
+  auto tstore = [&](const CUtensorMap* m, int col, int row, const void* src) {
+    if (CM) tma_store_2d(m, row, col, src);
+    else tma_store_2d(m, col, row, src);
+  };
 
   // right-hand side jw of the CTA: its plane, its barriers, and the copy of chunk k of work item it2 into its slot.
   // The copies and the tensor stores of a right-hand side are issued by one thread: lane 0 of its io warp
@@ -143,7 +166,7 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
   auto load_x = [&](int it2, int k, int c0_2, int xrow_2) {
     const int sl = slot(k, it2);
     mbar_expect_tx(&plxj[sl], CHUNK_BYTES);
-    tma_load_2d_hint(PXj + (size_t)sl * CH, &mx, c0_2, xrow_2 + k * LB, &plxj[sl], pol_stream);
+    tload_hint(PXj + (size_t)sl * CH, &mx, c0_2, xrow_2 + k * LB, &plxj[sl], pol_stream);
   };
   constexpr int kSD = 3;  // a slot is refilled kSD steps after its tensor store was committed (wait_group.read<kSD>)
   const int jb0 = ntail ? 1 : 0;  // the partial top chunk (back-substitution step 0) leaves by plain stores
@@ -179,14 +202,14 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         mbar_wait(&ready[s], rph);
         EKB_TICK(1)
         ring_advance();
-        const V* rm = RING + (size_t)s * 2 * CH + lane;
-        V* px = PXj + (size_t)sl * CH + lane;
+        const V* rm = RING + (size_t)s * 2 * CH;
+        V* px = PXj + (size_t)sl * CH;
         V m[LB], r[LB], x[LB];
 #pragma unroll
         for (int u = 0; u < LB; ++u) {
-          m[u] = rm[u * 32];
-          if (!EXACT) r[u] = rm[CH + u * 32];
-          x[u] = px[u * 32];
+          m[u] = ld(rm, u);
+          if (!EXACT) r[u] = ld(rm + CH, u);
+          x[u] = ld(px, u);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&freeb[s]);
@@ -205,7 +228,7 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
           }
         }
 #pragma unroll
-        for (int u = 0; u < LB; ++u) px[u * 32] = x[u];
+        for (int u = 0; u < LB; ++u) stv(px, u, x[u]);
         EKB_TICK(3)
       }
       // ------------------------------------------------------------ back substitution
@@ -222,17 +245,17 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
           ring_advance();
         }
         EKB_TICK(4)
-        const V* bu = RING + (size_t)s * 2 * CH + lane;  // EXACT: du of this chunk, re-read through L2
-        const V* pc = PC + (size_t)sl * CH + lane;
-        V* px = PXj + (size_t)sl * CH + lane;
+        const V* bu = RING + (size_t)s * 2 * CH;  // EXACT: du of this chunk, re-read through L2
+        const V* pc = PC + (size_t)sl * CH;
+        V* px = PXj + (size_t)sl * CH;
         V y[LB], c[LB], ui[LB], rr[LB];
 #pragma unroll
         for (int u = 0; u < LB; ++u) {
-          y[u] = px[u * 32];
-          c[u] = pc[u * 32];
+          y[u] = ld(px, u);
+          c[u] = ld(pc, u);
           if (EXACT) {
-            ui[u] = bu[u * 32];
-            rr[u] = bu[CH + u * 32];  // rcp_refined(d') from the factor warp
+            ui[u] = ld(bu, u);
+            rr[u] = ld(bu + CH, u);  // rcp_refined(d') from the factor warp
           }
         }
         __syncwarp();
@@ -258,10 +281,18 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
                 }
                 o.v[j] = xv[j];
               }
-              R* g = X + (size_t)(xrow0 + k * LB + u) * x_stride + col;
+              if (CM) {  // column-major: a column's levels are contiguous (only this ragged chunk goes uncoalesced)
 #pragma unroll
-              for (int j = 0; j < CPT; ++j)
-                if (col + j < ncol) __stcs(g + j, o.v[j]);
+                for (int j = 0; j < CPT; ++j) {
+                  const int64_t cj = (int64_t)c0 + j * 32 + lane;
+                  if (cj < ncol) __stcs(X + (size_t)cj * x_stride + (k * LB + u), o.v[j]);
+                }
+              } else {
+                R* g = X + (size_t)(xrow0 + k * LB + u) * x_stride + col;
+#pragma unroll
+                for (int j = 0; j < CPT; ++j)
+                  if (col + j < ncol) __stcs(g + j, o.v[j]);
+              }
             }
           }
           if (lane == 0) {  // every lane read its part of the slot before the __syncwarp above
@@ -308,14 +339,14 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
             }
           }
 #pragma unroll
-          for (int u = 0; u < LB; ++u) px[u * 32] = y[u];
+          for (int u = 0; u < LB; ++u) stv(px, u, y[u]);
           EKB_TICK(6)
           fence_proxy_async();  // generic-proxy writes of this chunk -> visible to the TMA store
           __syncwarp();
           EKB_TICK(7)
           if (lane == 0 && io) mbar_arrive(&xdonej[sl]);  // the io warp stores the slot and refills it
           if (lane == 0 && !io) {
-            tma_store_2d(&mx, c0, xrow0 + k * LB, PXj + (size_t)sl * CH);
+            tstore(&mx, c0, xrow0 + k * LB, PXj + (size_t)sl * CH);
             EKB_TICK(8)
             tma_store_commit();
             EKB_TICK(9)
@@ -369,15 +400,15 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
           w_raw += tb - ta;
           w_plc += clock64() - tb;
         }
-        V* r0 = RING + (size_t)s * 2 * CH + lane;
+        V* r0 = RING + (size_t)s * 2 * CH;
         V* r1 = r0 + CH;
-        V* pc = PC + (size_t)sl * CH + lane;
+        V* pc = PC + (size_t)sl * CH;
         V a[LB], b[LB], c[LB], om[LB], o1[LB], oc[LB];
 #pragma unroll
         for (int u = 0; u < LB; ++u) {
-          a[u] = r0[u * 32];
-          b[u] = EXACT ? pc[u * 32] : r1[u * 32];
-          c[u] = EXACT ? r1[u * 32] : pc[u * 32];
+          a[u] = ld(r0, u);
+          b[u] = EXACT ? ld(pc, u) : ld(r1, u);
+          c[u] = EXACT ? ld(r1, u) : ld(pc, u);
         }
         if (EXACT) {
           R sd[CPT], su[CPT];
@@ -427,9 +458,9 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         }
 #pragma unroll
         for (int u = 0; u < LB; ++u) {
-          r0[u * 32] = om[u];
-          if (!EXACT) r1[u * 32] = o1[u];
-          pc[u * 32] = oc[u];
+          stv(r0, u, om[u]);
+          if (!EXACT) stv(r1, u, o1[u]);
+          stv(pc, u, oc[u]);
         }
         fence_proxy_async();  // these slots are later overwritten by TMA copies
         __syncwarp();
@@ -448,11 +479,11 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         // solver warp
         for (int jb = 0; jb < nch; ++jb) {
           const int s = rs, sl = slot(nch - 1 - jb, it);
-          const V* pc = PC + (size_t)sl * CH + lane;
-          V* r1 = RING + (size_t)s * 2 * CH + CH + lane;
+          const V* pc = PC + (size_t)sl * CH;
+          V* r1 = RING + (size_t)s * 2 * CH + CH;
           V dd[LB];
 #pragma unroll
-          for (int u = 0; u < LB; ++u) dd[u] = pc[u * 32];
+          for (int u = 0; u < LB; ++u) dd[u] = ld(pc, u);
 #pragma unroll
           for (int u = 0; u < LB; ++u) {
 #pragma unroll
@@ -461,7 +492,7 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
           mbar_wait(&raw[s], rph);  // du has landed in the first half; the stage is ours until `ready`
           ring_advance();
 #pragma unroll
-          for (int u = 0; u < LB; ++u) r1[u * 32] = dd[u];
+          for (int u = 0; u < LB; ++u) stv(r1, u, dd[u]);
           fence_proxy_async();
           __syncwarp();
           if (lane == 0) mbar_arrive(&ready[s]);
@@ -482,11 +513,11 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
           V* st = RING + (size_t)s * 2 * CH;
           if (k < nch) {
             mbar_expect_tx(&raw[s], 2u * CHUNK_BYTES);
-            tma_load_2d(st, &mdl, c0, k * LB, &raw[s]);
-            tma_load_2d(st + CH, EXACT ? &mdu : &md, c0, k * LB, &raw[s]);
+            tload(st, &mdl, c0, k * LB, &raw[s]);
+            tload(st + CH, EXACT ? &mdu : &md, c0, k * LB, &raw[s]);
           } else {  // EXACT: du of chunk 2*nch-1-k for the back-substitution (an L2 hit)
             mbar_expect_tx(&raw[s], CHUNK_BYTES);
-            tma_load_2d(st, &mdu, c0, (2 * nch - 1 - k) * LB, &raw[s]);
+            tload(st, &mdu, c0, (2 * nch - 1 - k) * LB, &raw[s]);
           }
         }
       }
@@ -497,7 +528,7 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
       auto load_c = [&](int it2, int k) {
         const int sl = slot(k, it2);
         mbar_expect_tx(&plc[sl], CHUNK_BYTES);
-        tma_load_2d(PC + (size_t)sl * CH, EXACT ? &md : &mdu, item_c0(it2), k * LB, &plc[sl]);
+        tload(PC + (size_t)sl * CH, EXACT ? &md : &mdu, item_c0(it2), k * LB, &plc[sl]);
       };
       for (int k = 0; k < nch; ++k) load_c(0, k);
       for (int it = 0; it + 1 < nit; ++it)
@@ -519,7 +550,7 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         if (k == nfull) {  // partial top chunk: already stored by the solver warp
           if (has1) load_x(it + 1, jb, c0_n1, xrow_n1);
         } else {
-          tma_store_2d(&mx, c0, xrow0 + k * LB, PXj + (size_t)sl * CH);
+          tstore(&mx, c0, xrow0 + k * LB, PXj + (size_t)sl * CH);
           tma_store_commit();
           if (jb - jb0 >= kSD) {
             tma_store_wait_read<kSD>();
@@ -535,16 +566,21 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
 }
 
 // ------------------------------------------------------------------------------------------- host side
-template <typename R, bool EXACT, bool DBG>
+template <typename R, bool EXACT, bool DBG, bool CM>
 static int launch_shared_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nrhs, int64_t a_stride, int64_t x_stride,
                              int rh, int ns, size_t smem, cudaStream_t stream, const char* name) {
   constexpr int CPT = TmaCfg<R>::CPT, RN = EXACT ? 1 : TmaCfg<R>::RN, W = 32 * CPT;
   CUtensorMap mdl, md, mdu, mx;
+  if (CM) {  // [ncol][stride] rows whose first nlev entries are the column; 64-byte rows, swizzled (f64 only)
+    if (!make_tensor_map_2d<R>(&mdl, dl, nlev, ncol, a_stride, kLB, W, 1) || !make_tensor_map_2d<R>(&md, d, nlev, ncol, a_stride, kLB, W, 1) ||
+        !make_tensor_map_2d<R>(&mdu, du, nlev, ncol, a_stride, kLB, W, 1) || !make_tensor_map_2d<R>(&mx, X, nlev, ncol, x_stride, kLB, W, 1))
+      return EKAT_B200_ERR_UNSUPPORTED;
+  } else
   if (!make_tensor_map_2d<R>(&mdl, dl, ncol, nlev, a_stride, W, kLB, 0) || !make_tensor_map_2d<R>(&md, d, ncol, nlev, a_stride, W, kLB, 0) ||
       !make_tensor_map_2d<R>(&mdu, du, ncol, nlev, a_stride, W, kLB, 0) ||
       !make_tensor_map_2d<R>(&mx, X, ncol, (int64_t)nrhs * nlev, x_stride, W, kLB, 0))
     return EKAT_B200_ERR_UNSUPPORTED;
-  auto k = k_tridiag_tma_shared<R, EXACT, CPT, RN, DBG>;
+  auto k = k_tridiag_tma_shared<R, EXACT, CPT, RN, DBG, CM>;
   int rc = allow_smem(k, smem);
   if (rc) return rc;
   const int ngroups = nrhs / rh;
@@ -562,9 +598,10 @@ static int launch_shared_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, i
 
 // Returns EKAT_B200_ERR_UNSUPPORTED when the operands do not meet TMA's requirements or a tile does not fit on
 // chip; the caller then uses the cp.async kernels.
-template <typename R>
-int tridiag_tma_shared(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nrhs, int64_t a_stride,
-                       int64_t x_stride, cudaStream_t stream) {
+template <typename R, bool CM>
+static int run_shared(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nrhs, int64_t a_stride,
+                      int64_t x_stride, cudaStream_t stream) {
+  if (CM && (nrhs != 1 || sizeof(R) != 8)) return EKAT_B200_ERR_UNSUPPORTED;  // right-hand sides interleave within a column there
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
   if (!al(dl) || !al(d) || !al(du) || !al(X) || (a_stride * sizeof(R)) % 16 || (x_stride * sizeof(R)) % 16)
     return EKAT_B200_ERR_UNSUPPORTED;
@@ -574,7 +611,8 @@ int tridiag_tma_shared(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int n
   const int nch = (nlev + kLB - 1) / kLB, nslot = nch;
   const size_t chunk = (size_t)kLB * W * sizeof(R);
   auto smem_for = [&](int rh, int ns) {
-    const size_t bars = ((size_t)(3 * ns + (2 + 2 * rh) * nslot) * 8 + 127) & ~(size_t)127;
+    const size_t al_b = CM ? 1024 : 128;
+    const size_t bars = ((size_t)(3 * ns + (2 + 2 * rh) * nslot) * 8 + al_b - 1) & ~(al_b - 1);
     return bars + (size_t)(1 + rh) * nslot * chunk + (size_t)ns * 2 * chunk;
   };
   // right-hand sides per CTA: the largest divisor of nrhs whose planes fit next to a ring of >= 4 stages (>= 2 if none does)
@@ -595,13 +633,27 @@ int tridiag_tma_shared(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int n
   if (tu.prefetch >= 2 && tu.prefetch <= ns) ns = tu.prefetch;  // tuning override: ring stages
   const size_t smem = smem_for(rh, ns);
   const bool f64 = sizeof(R) == 8;
-  const char* name = exact ? (f64 ? "tridiag_tma_shared<f64,bfb>" : "tridiag_tma_shared<f32,bfb>")
-                           : (f64 ? "tridiag_tma_shared<f64,thomas>" : "tridiag_tma_shared<f32,thomas>");
-  if (tu.variant == 7)  // instrumented instantiation (phase trace)
-    return exact ? launch_shared_tma<R, true, true>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name)
-                 : launch_shared_tma<R, false, true>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name);
-  return exact ? launch_shared_tma<R, true, false>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name)
-               : launch_shared_tma<R, false, false>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name);
+  const char* name = CM ? (exact ? "tridiag_tma_shared_cm<f64,bfb>" : "tridiag_tma_shared_cm<f64,thomas>")
+                        : exact ? (f64 ? "tridiag_tma_shared<f64,bfb>" : "tridiag_tma_shared<f32,bfb>")
+                                : (f64 ? "tridiag_tma_shared<f64,thomas>" : "tridiag_tma_shared<f32,thomas>");
+  if (tu.variant == 7 && !CM)  // instrumented instantiation (phase trace)
+    return exact ? launch_shared_tma<R, true, true, false>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name)
+                 : launch_shared_tma<R, false, true, false>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name);
+  return exact ? launch_shared_tma<R, true, false, CM>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name)
+               : launch_shared_tma<R, false, false, CM>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name);
+}
+
+// level-major operands: dl,d,du [nlev][a_stride], X [nrhs][nlev][x_stride]
+template <typename R>
+int tridiag_tma_shared(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nrhs, int64_t a_stride,
+                       int64_t x_stride, cudaStream_t stream) {
+  return run_shared<R, false>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
+}
+// the reference's column-major operands, one right-hand side (f64): dl,d,du [ncol][a_stride], X [ncol][x_stride]
+template <typename R>
+int tridiag_tma_shared_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride,
+                          cudaStream_t stream) {
+  return run_shared<R, true>(exact, dl, d, du, X, ncol, nlev, 1, a_stride, x_stride, stream);
 }
 
 int debug_trace(long long* out, int n) {
@@ -612,5 +664,7 @@ int debug_trace(long long* out, int n) {
 
 template int tridiag_tma_shared<double>(bool, double*, double*, double*, double*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
 template int tridiag_tma_shared<float>(bool, float*, float*, float*, float*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
+template int tridiag_tma_shared_cm<double>(bool, double*, double*, double*, double*, int64_t, int, int64_t, int64_t, cudaStream_t);
+template int tridiag_tma_shared_cm<float>(bool, float*, float*, float*, float*, int64_t, int, int64_t, int64_t, cudaStream_t);
 
 }  // namespace ekb
