@@ -43,26 +43,50 @@ __device__ __forceinline__ float lds_at(unsigned addr, float) {
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
   return v;
 }
-// The running position is a 32-bit shared-memory byte address, so that a probe is exactly: load [p + const],
-// compare, predicated add (generic 64-bit pointers cost the compiler five extra instructions per probe).
+// The running position is a 32-bit shared-memory byte address and a probe is spelled in PTX as exactly: load
+// [p + const], compare, predicated add (left to itself the compiler emits an add, a compare and a predicated move,
+// and five more instructions per probe for generic 64-bit pointers). Returns the BYTE offset of the bracket k1
+// within the column (k1 * sizeof(R)): every later gather is [column base + offset] with no index arithmetic.
+template <int OFF, int STEP>
+__device__ __forceinline__ void probe(unsigned& p, double v) {
+  asm("{\n.reg .pred q;\n.reg .f64 t;\nld.shared.f64 t, [%0+%2];\nsetp.ge.f64 q, %1, t;\n@q add.u32 %0, %0, %3;\n}\n"
+      : "+r"(p)
+      : "d"(v), "n"(OFF), "n"(STEP));
+}
+template <int OFF, int STEP>
+__device__ __forceinline__ void probe(unsigned& p, float v) {
+  asm("{\n.reg .pred q;\n.reg .f32 t;\nld.shared.f32 t, [%0+%2];\nsetp.ge.f32 q, %1, t;\n@q add.u32 %0, %0, %3;\n}\n"
+      : "+r"(p)
+      : "f"(v), "n"(OFF), "n"(STEP));
+}
+template <typename R, int BIT>
+struct Probes {  // probes with steps 2^BIT, 2^(BIT-1), ..., 1 elements: the window [p, p + 2^(BIT+1)) shrinks to one slot
+  static __device__ __forceinline__ void run(unsigned& p, R v) {
+    constexpr int B = sizeof(R);
+    probe<((1 << BIT) - 1) * B, B << BIT>(p, v);
+    Probes<R, BIT - 1>::run(p, v);
+  }
+};
+template <typename R>
+struct Probes<R, -1> {
+  static __device__ __forceinline__ void run(unsigned&, R) {}
+};
 template <typename R, int LOG2P>
-__device__ __forceinline__ int bracket(unsigned x1, int km1, int P, R v) {
+__device__ __forceinline__ unsigned bracket_off(unsigned x1, int km1, int P, R v) {
   constexpr unsigned B = sizeof(R);
   unsigned p = x1;
   if (km1 > P) {
     if (v >= lds_at(x1 + (unsigned)(km1 - P - 1) * B, R())) p += (unsigned)(km1 - P) * B;
   }
   if (LOG2P > 0) {
-#pragma unroll
-    for (int b = LOG2P - 1; b >= 0; --b)
-      if (v >= lds_at(p + ((1u << b) - 1u) * B, R())) p += B << b;
+    Probes<R, LOG2P - 1>::run(p, v);  // LOG2P probes: steps P/2 ... 1
   } else {
     for (int step = P >> 1; step >= 1; step >>= 1)
       if (v >= lds_at(p + (unsigned)(step - 1) * B, R())) p += (unsigned)step * B;
   }
-  if (v >= lds_at(p, R())) p += B;
-  const int pos = (int)((p - x1) / B);
-  return pos > 0 ? pos - 1 : pos;
+  probe<0, B>(p, v);  // the last slot itself
+  // pos = (p - x1) / B entries are <= v; the reference's "if (idx > 0) --idx" (ekat_lin_interp_impl.hpp:179-181)
+  return max(p - x1, B) - B;
 }
 
 struct LiArgs {
@@ -105,13 +129,14 @@ __global__ void __launch_bounds__(256) k_lin_interp(const LiArgs a) {
   // issue the loads of tile `tile` into stage `s` (TMA when the tile is full and aligned)
   auto issue = [&](int64_t tile, int s) {
     const int64_t c0 = tile * CB;
+    const bool tma = a.use_tma && c0 + CB <= a.ncol;
+    if (tma && tid != 0) return true;  // one thread feeds the copy engine; nobody else spends an instruction here
     const int nc = (int)tmin<int64_t>(CB, a.ncol - c0);
     R* sx1 = stage0 + (size_t)s * stage_elems;
     R* sy1 = sx1 + n1p;
     R* sx2 = sy1 + n1p * nf;
-    const bool tma = a.use_tma && nc == CB;
     if (tma) {
-      if (tid == 0) {
+      {
         fence_proxy_async();
         const unsigned b1 = (unsigned)(n1 * sizeof(R)), b2 = (unsigned)(n2 * sizeof(R));
         mbar_expect_tx(&bars[s], b1 * (1 + nf) + (need_x2 ? b2 : 0));
@@ -156,39 +181,41 @@ __global__ void __launch_bounds__(256) k_lin_interp(const LiArgs a) {
     const R* sx1 = stage0 + (size_t)s * stage_elems;
     const R* sy1 = sx1 + n1p;
     const R* sx2 = sy1 + n1p * nf;
-    // one warp per column (CB is a multiple of the warp count whenever a stage can hold that many columns):
-    // per-column addresses are formed once, lanes walk the targets 32 at a time
+    // one warp per column (CB is a multiple of the warp count whenever a stage can hold that many columns); lanes walk
+    // the targets 32 at a time. Everything per target is [32-bit shared address + byte offset]: per-column bases are
+    // formed once, the loop carries three running pointers and no index arithmetic.
     const int p1 = (int)a.pitch1, p2 = (int)a.pitch2, P = a.P;
+    constexpr unsigned B = sizeof(R);
+    const unsigned last_off = (unsigned)(km1 - 1) * B;
+    const bool want_map = MODE != LI_APPLY && a.indx != nullptr;
     for (int c = warp; c < nc; c += nwarp) {
-      const R* x1c = sx1 + c * p1;
-      const R* x2c = sx2 + c * p2;
-      const unsigned x1a = smem_u32(x1c);
-      const R* y1c0 = sy1 + c * p1;
+      const unsigned x1a = smem_u32(sx1 + c * p1), y1a = smem_u32(sy1 + c * p1);
+      unsigned x2a = smem_u32(sx2 + c * p2) + (unsigned)lane * B;
       const size_t gcol = (size_t)(c0 + c);
-      R* gyc = gy2 + gcol * p2;
-      int* gic = (MODE != LI_APPLY && a.indx) ? a.indx + gcol * km2 : nullptr;
-      const int* gin = MODE == LI_APPLY ? a.indx_in + gcol * km2 : nullptr;
-      for (int k2 = lane; k2 < km2; k2 += 32) {
-        const R xt = x2c[k2];
-        int k1;
-        if (MODE == LI_APPLY) k1 = gin[k2];
-        else k1 = bracket<R, LOG2P>(x1a, km1, P, xt);
-        if (gic) gic[k2] = k1;
+      R* gy = gy2 + gcol * p2 + lane;
+      int* gi = want_map ? a.indx + gcol * km2 + lane : nullptr;
+      const int* gin = MODE == LI_APPLY ? a.indx_in + gcol * km2 + lane : nullptr;
+      for (int k2 = lane; k2 < km2; k2 += 32, x2a += 32 * B, gy += 32) {
+        const R xt = lds_at(x2a, R());
+        unsigned off;  // byte offset of the bracket k1 within the column
+        if (MODE == LI_APPLY) off = (unsigned)gin[k2 - lane] * B;
+        else off = bracket_off<R, LOG2P>(x1a, km1, P, xt);
+        if (want_map) gi[k2 - lane] = (int)(off / B);
         if (MODE != LI_SETUP) {
-          const int k1ph = k1 == km1 - 1 ? k1 - 1 : k1 + 1;  // :119-131
-          const R xa = x1c[k1], xb = x1c[k1ph];
+          const unsigned offph = off == last_off ? off - B : off + B;  // k1ph, :119-131
+          const R xa = lds_at(x1a + off, R()), xb = lds_at(x1a + offph, R());
           const R dxt = x_sub(xt, xa), dx = x_sub(xb, xa);
-          const R* y1c = y1c0;
-          R* gy = gyc + k2;
+          unsigned yf = y1a;
+          R* gyf = gy;
           for (int f = 0; f < nf; ++f) {
-            const R ya = y1c[k1], yb = y1c[k1ph];
+            const R ya = lds_at(yf + off, R()), yb = lds_at(yf + offph, R());
             R v = x_sub(yb, ya);  // :153
             v = x_mul(v, dxt);    // :154
             v = x_div(v, dx);     // :155
             v = x_add(v, ya);     // :156
-            st_stream(gy, v);
-            y1c += n1p;
-            gy += a.y2_fstride;
+            st_stream(gyf, v);
+            yf += (unsigned)(n1p * B);
+            gyf += a.y2_fstride;
           }
         }
       }
@@ -209,9 +236,11 @@ int lin_interp(int mode, const R* x1, const R* x2, const R* y1, R* y2, int* indx
   }
   const int nf = mode == LI_SETUP ? 0 : nfields;
   const size_t col_bytes = ((size_t)pitch1 * (1 + nf) + pitch2) * sizeof(R);
-  // columns per tile: ~24 KB stages so that 3+ CTAs (2 stages each) share an SM
+  // columns per tile: a multiple of the 8 warps, stages of at most ~36 KB (2-4 CTAs of 2 stages each per SM) and at
+  // most 24 columns (measured, f64 / f32: 72->128 best at 16 / 24 columns, 128->128 at 8 / 16)
   const Tuning tu = tuning();
-  int CB = tu.cols_per_cta > 0 ? tu.cols_per_cta : (int)((24 * 1024) / col_bytes);
+  int CB = tu.cols_per_cta > 0 ? tu.cols_per_cta : (int)((36 * 1024) / col_bytes);
+  if (tu.cols_per_cta <= 0 && CB > 24) CB = 24;
   if (CB > 64) CB = 64;
   if (tu.cols_per_cta <= 0) CB = CB >= 8 ? (CB & ~7) : 8;  // a multiple of the 8 warps: one column per warp per round
   if (CB > 1) CB &= ~1;  // even -> tile byte counts are multiples of 16 for f64

@@ -152,6 +152,12 @@ if __name__ == "__main__":
         tridiag_case("bfb", "f64", 345600, 72, tunings=[(0, 0, 0), (2, 0, 0), (3, 0, 0), (4, 0, 0)])
         tridiag_case("bfb", "f64", 345600, 128, layout=ekat_b200.COL_MAJOR, tunings=[(0, 0, 0), (2, 0, 0), (3, 0, 0), (0, 0, 4)])
         tridiag_case("bfb", "f64", 345600, 128, 10, 10)
+    if "licb" in what:
+        for km1 in (72, 128):
+            li_case("f64", 345600, km1, 128, 1, tunings=[(8, 0, 0), (12, 0, 0), (16, 0, 0), (20, 0, 0), (24, 0, 0)])
+            li_case("f32", 345600, km1, 128, 1, tunings=[(8, 0, 0), (16, 0, 0), (24, 0, 0), (32, 0, 0), (48, 0, 0)])
+        li_case("f64", 3145728, 128, 128, 1, tunings=[(8, 0, 0), (16, 0, 0)])
+        li_case("f64", 345600, 72, 128, 16, tunings=[(8, 0, 0), (16, 0, 0)])
     if "c1" in what:
         for s in ("thomas", "bfb", "cr"):
             tridiag_case(s, "f64", 21600, 72, tunings=[(0, 0, 0), (16, 8, 0), (16, 16, 0), (32, 8, 0), (64, 16, 0)])
