@@ -26,6 +26,9 @@ int lin_interp(int mode, const R* x1, const R* x2, const R* y1, R* y2, int* indx
                int km1, int km2, int64_t pitch1, int64_t pitch2, int nfields, int64_t y1_fstride, int64_t y2_fstride,
                cudaStream_t stream);
 template <typename R>
+int lin_interp_lm(const R* x1, const R* x2, const R* y1, R* y2, int64_t ncol, int km1, int km2, int64_t pitch, int nfields,
+                  cudaStream_t stream);
+template <typename R>
 int tridiag_lin_interp(const R* dl, const R* d, const R* du, const R* B, const R* x1, const R* x2, R* Y2, R* X,
                        int64_t ncol, int nlev, int km2, int nrhs, int64_t pitch, cudaStream_t stream);
 template <typename R>
@@ -174,6 +177,17 @@ DEF_LI(float, f32)
   }
 DEF_FUSED(double, f64)
 DEF_FUSED(float, f32)
+
+#define DEF_LI_LM(T, sfx)                                                                                      \
+  int ekat_b200_lin_interp_lm_##sfx(const T* x1, const T* x2, const T* y1, T* y2, int64_t ncol, int km1,       \
+                                    int km2, int64_t pitch, int nfields, ekat_b200_stream_t stream) {          \
+    if (ncol < 0 || km1 < 0 || km2 < 0 || nfields < 0) return EKAT_B200_ERR_INVALID;                           \
+    if (ncol == 0 || km2 == 0 || nfields == 0) return EKAT_B200_OK;                                            \
+    if (km1 < 2 || pitch < ncol || !x1 || !x2 || !y1 || !y2) return EKAT_B200_ERR_INVALID;                     \
+    return lin_interp_lm<T>(x1, x2, y1, y2, ncol, km1, km2, pitch, nfields, ST(stream));                       \
+  }
+DEF_LI_LM(double, f64)
+DEF_LI_LM(float, f32)
 
 #define DEF_UTIL(T, sfx)                                                                                       \
   int ekat_b200_col_to_lev_##sfx(const T* src, T* dst, int64_t ncol, int n, int64_t src_stride, int64_t pitch, \

@@ -134,9 +134,28 @@ static int launch_fused(const R* dl, const R* d, const R* du, const R* B, const 
 }
 
 template <typename R>
+int tridiag_tma_shared_oop(bool exact, R* dl, R* d, R* du, const R* B, R* X, int64_t ncol, int nlev, int nrhs,
+                           int64_t a_stride, int64_t x_stride, cudaStream_t stream);
+template <typename R>
+int lin_interp_lm(const R* x1, const R* x2, const R* y1, R* y2, int64_t ncol, int km1, int km2, int64_t pitch, int nfields,
+                  cudaStream_t stream);
+
+template <typename R>
 int tridiag_lin_interp(const R* dl, const R* d, const R* du, const R* B, const R* x1, const R* x2, R* Y2, R* X,
                        int64_t ncol, int nlev, int km2, int nrhs, int64_t pitch, cudaStream_t stream) {
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  // Fast path: the persistent TMA solve (B -> X, out of place) followed by the level-major interpolation (X -> Y2),
+  // both at their own HBM roofline. The solutions make one round trip through HBM/L2 between the two; when the
+  // caller does not ask for them (X == nullptr) they are staged in Y2 itself, which has their shape when
+  // km2 == nlev, and interpolated in place tile by tile. The one-kernel version below keeps them on chip but
+  // holds only 16 columns per SM and runs at a fifth of this speed (profiles/).
+  if (tuning().variant == 0 && km2 > 0 && (X != nullptr || km2 == nlev)) {
+    R* sol = X ? X : Y2;
+    int rc = tridiag_tma_shared_oop<R>(false, const_cast<R*>(dl), const_cast<R*>(d), const_cast<R*>(du), B, sol, ncol, nlev,
+                                       nrhs, pitch, pitch, stream);
+    if (rc == EKAT_B200_OK) rc = lin_interp_lm<R>(x1, x2, sol, Y2, ncol, nlev, km2, pitch, nrhs, stream);
+    if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+  }
   constexpr int VEC = 16 / sizeof(R);
   const bool vec = al(dl) && al(d) && al(du) && al(B) && (X == nullptr || al(X)) && (pitch * sizeof(R)) % 16 == 0;
   return vec ? launch_fused<R, VEC>(dl, d, du, B, x1, x2, Y2, X, ncol, nlev, km2, nrhs, pitch, stream)

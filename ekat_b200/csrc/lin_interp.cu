@@ -22,72 +22,11 @@
 #include <cstdio>
 #include <cstdlib>
 
-#include "common.cuh"
+#include "lin_interp_search.cuh"
 
 namespace ekb {
 
 enum LiMode { LI_FUSED = 0, LI_SETUP = 1, LI_APPLY = 2 };
-
-// upper_bound over sorted x1[0..km1): the number of entries <= v, found with the reference's predicate
-// `v >= *it` (ekat_upper_bound.hpp:37-48), so ties and NaNs resolve identically; then the reference's
-// "if (idx > 0) --idx" (:179-181). Branch-free: one probe picks the power-of-two window [0,P) or [km1-P,km1)
-// (P = bit_floor(km1)) that must contain the boundary, then log2(P) probes with halving steps and a last one --
-// each a shared-memory load, a compare and a predicated add. LOG2P > 0: unrolled for that window; 0: loop.
-__device__ __forceinline__ double lds_at(unsigned addr, double) {
-  double v;
-  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
-  return v;
-}
-__device__ __forceinline__ float lds_at(unsigned addr, float) {
-  float v;
-  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
-  return v;
-}
-// The running position is a 32-bit shared-memory byte address and a probe is spelled in PTX as exactly: load
-// [p + const], compare, predicated add (left to itself the compiler emits an add, a compare and a predicated move,
-// and five more instructions per probe for generic 64-bit pointers). Returns the BYTE offset of the bracket k1
-// within the column (k1 * sizeof(R)): every later gather is [column base + offset] with no index arithmetic.
-template <int OFF, int STEP>
-__device__ __forceinline__ void probe(unsigned& p, double v) {
-  asm("{\n.reg .pred q;\n.reg .f64 t;\nld.shared.f64 t, [%0+%2];\nsetp.ge.f64 q, %1, t;\n@q add.u32 %0, %0, %3;\n}\n"
-      : "+r"(p)
-      : "d"(v), "n"(OFF), "n"(STEP));
-}
-template <int OFF, int STEP>
-__device__ __forceinline__ void probe(unsigned& p, float v) {
-  asm("{\n.reg .pred q;\n.reg .f32 t;\nld.shared.f32 t, [%0+%2];\nsetp.ge.f32 q, %1, t;\n@q add.u32 %0, %0, %3;\n}\n"
-      : "+r"(p)
-      : "f"(v), "n"(OFF), "n"(STEP));
-}
-template <typename R, int BIT>
-struct Probes {  // probes with steps 2^BIT, 2^(BIT-1), ..., 1 elements: the window [p, p + 2^(BIT+1)) shrinks to one slot
-  static __device__ __forceinline__ void run(unsigned& p, R v) {
-    constexpr int B = sizeof(R);
-    probe<((1 << BIT) - 1) * B, B << BIT>(p, v);
-    Probes<R, BIT - 1>::run(p, v);
-  }
-};
-template <typename R>
-struct Probes<R, -1> {
-  static __device__ __forceinline__ void run(unsigned&, R) {}
-};
-template <typename R, int LOG2P>
-__device__ __forceinline__ unsigned bracket_off(unsigned x1, int km1, int P, R v) {
-  constexpr unsigned B = sizeof(R);
-  unsigned p = x1;
-  if (km1 > P) {
-    if (v >= lds_at(x1 + (unsigned)(km1 - P - 1) * B, R())) p += (unsigned)(km1 - P) * B;
-  }
-  if (LOG2P > 0) {
-    Probes<R, LOG2P - 1>::run(p, v);  // LOG2P probes: steps P/2 ... 1
-  } else {
-    for (int step = P >> 1; step >= 1; step >>= 1)
-      if (v >= lds_at(p + (unsigned)(step - 1) * B, R())) p += (unsigned)step * B;
-  }
-  probe<0, B>(p, v);  // the last slot itself
-  // pos = (p - x1) / B entries are <= v; the reference's "if (idx > 0) --idx" (ekat_lin_interp_impl.hpp:179-181)
-  return max(p - x1, B) - B;
-}
 
 struct LiArgs {
   const void *x1, *x2, *y1;
@@ -199,7 +138,7 @@ __global__ void __launch_bounds__(256) k_lin_interp(const LiArgs a) {
         const R xt = lds_at(x2a, R());
         unsigned off;  // byte offset of the bracket k1 within the column
         if (MODE == LI_APPLY) off = (unsigned)gin[k2 - lane] * B;
-        else off = bracket_off<R, LOG2P>(x1a, km1, P, xt);
+        else off = bracket_off<R, LOG2P, sizeof(R)>(x1a, km1, P, xt);
         if (want_map) gi[k2 - lane] = (int)(off / B);
         if (MODE != LI_SETUP) {
           const unsigned offph = off == last_off ? off - B : off + B;  // k1ph, :119-131

@@ -1,0 +1,149 @@
+// lin_interp_lm.cu -- fused bracket search + linear interpolation on LEVEL-MAJOR operands
+//     x1 [km1][pitch], x2 [km2][pitch], y1 [nfields][km1][pitch], y2 [nfields][km2][pitch]      (columns fastest)
+// the layout the tridiagonal kernels are native in, so that "diffuse then remap" (BASELINE config 4) needs no
+// transpose between the two. Same arithmetic as lin_interp.cu: the reference's predicate `v >= *it`
+// (src/kokkos/ekat_upper_bound.hpp:37-48), "if (idx > 0) --idx" (src/algorithm/ekat_lin_interp_impl.hpp:179-181) and
+// the four statements of :153-156 in order, unfused -> bit-identical to ekat::LinInterp for any pack size.
+//
+// A CTA owns a tile of 32 columns: lane = column, the 8 warps split the target levels. The tile's source coordinates
+// and one source field at a time (double-buffered) arrive by 2D TMA tensor copies as [level][32 columns], so a lane
+// only ever touches its own shared-memory bank (every gather is conflict-free whatever the brackets are), target
+// coordinates are read and results written as coalesced 256-byte rows, and the bracket of a target is searched once
+// and reused for every field (the reference's setup-once / interpolate-many contract, ekat_lin_interp.hpp:13-16).
+// y2 may alias y1 when km2 == km1: a field's tile is complete in shared memory before its targets are written.
+#include <cuda.h>
+
+#include "lin_interp_search.cuh"
+#include "tridiag_tma.cuh"
+
+namespace ekb {
+
+constexpr int kLmWarps = 8;
+
+// TW = tile width in columns (16 or 32): lane = (target parity, column) for TW = 16. NSY field stages in flight.
+template <typename R, int LOG2P, int TW>
+__global__ void __launch_bounds__(32 * kLmWarps)
+k_lin_interp_lm(const __grid_constant__ CUtensorMap mx1, const __grid_constant__ CUtensorMap my1, const R* __restrict__ x2,
+                R* __restrict__ y2, int64_t ncol, int km1, int km2, int64_t pitch, int nf, int P, int NSY) {
+  constexpr unsigned B = sizeof(R), ROW = TW * B;
+  constexpr int TPS = 32 / TW;  // targets per warp step
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);  // [0] x1 landed, [1 + s] field stage s landed
+  const size_t tile = (((size_t)km1 * ROW + 127) & ~(size_t)127) / B;  // elements per staged tile (TMA wants 128-byte aligned boxes)
+  R* sx1 = reinterpret_cast<R*>(smem_raw + 128);           // [km1][TW]
+  R* sy = sx1 + tile;                                      // [NSY][km1][TW]
+  unsigned short* smap = reinterpret_cast<unsigned short*>(sy + (size_t)NSY * tile);  // [km2][TW] brackets
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int lc = lane % TW, sub = lane / TW;
+  const int c0 = blockIdx.x * TW;
+  const int64_t col = (int64_t)c0 + lc;
+  const bool live = col < ncol;
+  const int64_t gcol = live ? col : ncol - 1;
+  const unsigned tile_bytes = (unsigned)km1 * ROW;
+
+  auto load_tile = [&](R* dst, const CUtensorMap* m, int row0, uint64_t* bar) {  // one box: km1 (<= 256) rows of TW columns
+    mbar_expect_tx(bar, tile_bytes);
+    tma_load_2d(dst, m, c0, row0, bar);
+  };
+  if (tid == 0) {
+    for (int s = 0; s <= NSY; ++s) mbar_init(&bars[s], 1);
+    fence_mbar_init();
+    load_tile(sx1, &mx1, 0, &bars[0]);
+    for (int f = 0; f < NSY && f < nf; ++f) load_tile(sy + (size_t)f * tile, &my1, f * km1, &bars[1 + f]);
+  }
+  __syncthreads();
+
+  // ---- setup: one bracket per (target level, column); each thread later reads back only what it wrote itself
+  const unsigned x1a = smem_u32(sx1) + (unsigned)lc * B;
+  mbar_wait(&bars[0], 0u);
+  for (int j = warp * TPS + sub; j < km2; j += kLmWarps * TPS) {
+    const R xt = __ldg(x2 + (size_t)j * pitch + gcol);
+    const unsigned off = bracket_off<R, LOG2P, ROW>(x1a, km1, P, xt);
+    smap[j * TW + lc] = (unsigned short)(off / ROW);
+  }
+
+  // ---- interpolation, field by field
+  const unsigned last_off = (unsigned)(km1 - 1) * ROW;
+  int s = 0;
+  unsigned ph = 0;
+  for (int f = 0; f < nf; ++f) {
+    mbar_wait(&bars[1 + s], ph);
+    const unsigned y1a = smem_u32(sy + (size_t)s * tile) + (unsigned)lc * B;
+    R* gy = y2 + ((size_t)f * km2) * pitch + col;
+    for (int j = warp * TPS + sub; j < km2; j += kLmWarps * TPS) {
+      const R xt = __ldg(x2 + (size_t)j * pitch + gcol);
+      const unsigned off = (unsigned)smap[j * TW + lc] * ROW;
+      const unsigned offph = off == last_off ? off - ROW : off + ROW;  // k1ph, :119-131
+      const R xa = lds_at(x1a + off, R()), xb = lds_at(x1a + offph, R());
+      const R ya = lds_at(y1a + off, R()), yb = lds_at(y1a + offph, R());
+      const R dxt = x_sub(xt, xa), dx = x_sub(xb, xa);
+      R v = x_sub(yb, ya);  // :153
+      v = x_mul(v, dxt);    // :154
+      v = x_div(v, dx);     // :155
+      v = x_add(v, ya);     // :156
+      if (live) st_stream(gy + (size_t)j * pitch, v);
+    }
+    __syncthreads();  // every warp is done with stage s
+    if (tid == 0 && f + NSY < nf) load_tile(sy + (size_t)s * tile, &my1, (f + NSY) * km1, &bars[1 + s]);
+    if (++s == NSY) {
+      s = 0;
+      ph ^= 1u;
+    }
+  }
+}
+
+// Returns EKAT_B200_ERR_UNSUPPORTED when the operands do not meet TMA's requirements or a tile does not fit on chip.
+template <typename R>
+int lin_interp_lm(const R* x1, const R* x2, const R* y1, R* y2, int64_t ncol, int km1, int km2, int64_t pitch, int nfields,
+                  cudaStream_t stream) {
+  if (ncol == 0 || km2 == 0 || nfields == 0) return EKAT_B200_OK;
+  auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  if (!al(x1) || !al(y1) || (pitch * sizeof(R)) % 16) return EKAT_B200_ERR_UNSUPPORTED;
+  if (ncol >= (int64_t)1 << 31 || (int64_t)nfields * km1 >= (int64_t)1 << 31 || km1 > 256) return EKAT_B200_ERR_UNSUPPORTED;  // one TMA box per tile
+  // tile width and field stages: 16-column tiles (128-byte rows for f64), two field stages -> 52 KB, four CTAs per SM;
+  // tuning: cols_per_cta = 16 | 32, prefetch = stages
+  const Tuning tu = tuning();
+  const int tw = tu.cols_per_cta == 32 ? 32 : 16;
+  int nsy = tu.prefetch >= 1 && tu.prefetch <= 8 ? tu.prefetch : 2;  // measured: residency (4 CTAs per SM) beats deeper staging
+  if (nsy > nfields) nsy = nfields;
+  auto smem_for = [&](int st) {
+    return 128 + (size_t)(1 + st) * (((size_t)km1 * tw * sizeof(R) + 127) & ~(size_t)127) + (size_t)km2 * tw * sizeof(unsigned short);
+  };
+  while (nsy > 1 && smem_for(nsy) > kMaxSmemPerCta / 2) --nsy;
+  const size_t smem = smem_for(nsy);
+  if (smem > kMaxSmemPerCta) return EKAT_B200_ERR_UNSUPPORTED;
+  CUtensorMap mx1, my1;
+  const int boxr = km1;
+  if (!make_tensor_map_2d<R>(&mx1, x1, ncol, km1, pitch, tw, boxr, 0) ||
+      !make_tensor_map_2d<R>(&my1, y1, ncol, (int64_t)nfields * km1, pitch, tw, boxr, 0))
+    return EKAT_B200_ERR_UNSUPPORTED;
+  int P = 1, log2p = 0;
+  while (2 * P <= km1) {
+    P *= 2;
+    ++log2p;
+  }
+  const unsigned grid = (unsigned)((ncol + tw - 1) / tw);
+  int rc;
+#define EKB_LM_LAUNCH2(L2_, TW_)                                                                       \
+  {                                                                                                    \
+    auto k = k_lin_interp_lm<R, L2_, TW_>;                                                             \
+    if ((rc = allow_smem(k, smem))) return rc;                                                         \
+    k<<<grid, 32 * kLmWarps, smem, stream>>>(mx1, my1, x2, y2, ncol, km1, km2, pitch, nfields, P, nsy); \
+  }
+#define EKB_LM_LAUNCH(L2_)            \
+  if (tw == 32) EKB_LM_LAUNCH2(L2_, 32) \
+  else EKB_LM_LAUNCH2(L2_, 16)
+  if (log2p == 6) EKB_LM_LAUNCH(6)
+  else if (log2p == 7) EKB_LM_LAUNCH(7)
+  else EKB_LM_LAUNCH(0)
+#undef EKB_LM_LAUNCH
+#undef EKB_LM_LAUNCH2
+  note_launch(sizeof(R) == 8 ? "lin_interp_lm<f64>" : "lin_interp_lm<f32>");
+  return check_cuda(cudaGetLastError());
+}
+
+template int lin_interp_lm<double>(const double*, const double*, const double*, double*, int64_t, int, int, int64_t, int, cudaStream_t);
+template int lin_interp_lm<float>(const float*, const float*, const float*, float*, int64_t, int, int, int64_t, int, cudaStream_t);
+
+}  // namespace ekb

@@ -83,8 +83,9 @@ __device__ __forceinline__ void trace_put(int it, int idx, long long v) {
 template <typename R, bool EXACT, int CPT, int RN, bool DBG, bool CM>
 __global__ void __launch_bounds__(512, 1)
 k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
-                     const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mx, R* __restrict__ X,
-                     int64_t ncol, int nlev, int64_t x_stride, int rh, int ngroups, int nwork, int NS, int io) {
+                     const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mx,
+                     const __grid_constant__ CUtensorMap mxin, R* __restrict__ X, int64_t ncol, int nlev, int64_t x_stride, int rh,
+                     int ngroups, int nwork, int NS, int io) {
   using V = Vec<R, CPT>;
   constexpr int LB = kLB, W = 32 * CPT, CH = LB * 32;
   constexpr unsigned CHUNK_BYTES = LB * W * sizeof(R);
@@ -166,7 +167,7 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
   auto load_x = [&](int it2, int k, int c0_2, int xrow_2) {
     const int sl = slot(k, it2);
     mbar_expect_tx(&plxj[sl], CHUNK_BYTES);
-    tload_hint(PXj + (size_t)sl * CH, &mx, c0_2, xrow_2 + k * LB, &plxj[sl], pol_stream);
+    tload_hint(PXj + (size_t)sl * CH, &mxin, c0_2, xrow_2 + k * LB, &plxj[sl], pol_stream);  // B (mxin) in, X (mx) out
   };
   constexpr int kSD = 3;  // a slot is refilled kSD steps after its tensor store was committed (wait_group.read<kSD>)
   const int jb0 = ntail ? 1 : 0;  // the partial top chunk (back-substitution step 0) leaves by plain stores
@@ -567,18 +568,20 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
 
 // ------------------------------------------------------------------------------------------- host side
 template <typename R, bool EXACT, bool DBG, bool CM>
-static int launch_shared_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nrhs, int64_t a_stride, int64_t x_stride,
+static int launch_shared_tma(R* dl, R* d, R* du, R* X, const R* Xin, int64_t ncol, int nlev, int nrhs, int64_t a_stride, int64_t x_stride,
                              int rh, int ns, size_t smem, cudaStream_t stream, const char* name) {
   constexpr int CPT = TmaCfg<R>::CPT, RN = EXACT ? 1 : TmaCfg<R>::RN, W = 32 * CPT;
-  CUtensorMap mdl, md, mdu, mx;
+  CUtensorMap mdl, md, mdu, mx, mxin;
   if (CM) {  // [ncol][stride] rows whose first nlev entries are the column; 64-byte rows, swizzled (f64 only)
     if (!make_tensor_map_2d<R>(&mdl, dl, nlev, ncol, a_stride, kLB, W, 1) || !make_tensor_map_2d<R>(&md, d, nlev, ncol, a_stride, kLB, W, 1) ||
-        !make_tensor_map_2d<R>(&mdu, du, nlev, ncol, a_stride, kLB, W, 1) || !make_tensor_map_2d<R>(&mx, X, nlev, ncol, x_stride, kLB, W, 1))
+        !make_tensor_map_2d<R>(&mdu, du, nlev, ncol, a_stride, kLB, W, 1) || !make_tensor_map_2d<R>(&mx, X, nlev, ncol, x_stride, kLB, W, 1) ||
+        !make_tensor_map_2d<R>(&mxin, Xin, nlev, ncol, x_stride, kLB, W, 1))
       return EKAT_B200_ERR_UNSUPPORTED;
   } else
   if (!make_tensor_map_2d<R>(&mdl, dl, ncol, nlev, a_stride, W, kLB, 0) || !make_tensor_map_2d<R>(&md, d, ncol, nlev, a_stride, W, kLB, 0) ||
       !make_tensor_map_2d<R>(&mdu, du, ncol, nlev, a_stride, W, kLB, 0) ||
-      !make_tensor_map_2d<R>(&mx, X, ncol, (int64_t)nrhs * nlev, x_stride, W, kLB, 0))
+      !make_tensor_map_2d<R>(&mx, X, ncol, (int64_t)nrhs * nlev, x_stride, W, kLB, 0) ||
+      !make_tensor_map_2d<R>(&mxin, Xin, ncol, (int64_t)nrhs * nlev, x_stride, W, kLB, 0))
     return EKAT_B200_ERR_UNSUPPORTED;
   auto k = k_tridiag_tma_shared<R, EXACT, CPT, RN, DBG, CM>;
   int rc = allow_smem(k, smem);
@@ -590,7 +593,7 @@ static int launch_shared_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, i
   const int64_t grid = tmin<int64_t>(nwork, (int64_t)kNumSms * tmax(1, per_sm));
   // one io warp per solver warp (TMA issue off the solver's critical path) while the block stays within 512 threads
   const int io = (2 * rh + 3) * 32 <= 512 && tuning().variant != 8 ? 1 : 0;
-  k<<<(unsigned)grid, 32 * (rh + 3 + (io ? rh : 0)), smem, stream>>>(mdl, md, mdu, mx, X, ncol, nlev, x_stride, rh, ngroups,
+  k<<<(unsigned)grid, 32 * (rh + 3 + (io ? rh : 0)), smem, stream>>>(mdl, md, mdu, mx, mxin, X, ncol, nlev, x_stride, rh, ngroups,
                                                                     (int)nwork, ns, io);
   note_launch(name);
   return check_cuda(cudaGetLastError());
@@ -599,11 +602,11 @@ static int launch_shared_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, i
 // Returns EKAT_B200_ERR_UNSUPPORTED when the operands do not meet TMA's requirements or a tile does not fit on
 // chip; the caller then uses the cp.async kernels.
 template <typename R, bool CM>
-static int run_shared(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nrhs, int64_t a_stride,
+static int run_shared(bool exact, R* dl, R* d, R* du, R* X, const R* Xin, int64_t ncol, int nlev, int nrhs, int64_t a_stride,
                       int64_t x_stride, cudaStream_t stream) {
   if (CM && (nrhs != 1 || sizeof(R) != 8)) return EKAT_B200_ERR_UNSUPPORTED;  // right-hand sides interleave within a column there
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
-  if (!al(dl) || !al(d) || !al(du) || !al(X) || (a_stride * sizeof(R)) % 16 || (x_stride * sizeof(R)) % 16)
+  if (!al(dl) || !al(d) || !al(du) || !al(X) || !al(Xin) || (a_stride * sizeof(R)) % 16 || (x_stride * sizeof(R)) % 16)
     return EKAT_B200_ERR_UNSUPPORTED;
   if (ncol >= (int64_t)1 << 31 || (int64_t)nrhs * nlev >= (int64_t)1 << 31) return EKAT_B200_ERR_UNSUPPORTED;
   constexpr int CPT = TmaCfg<R>::CPT, W = 32 * CPT;
@@ -637,23 +640,29 @@ static int run_shared(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nl
                         : exact ? (f64 ? "tridiag_tma_shared<f64,bfb>" : "tridiag_tma_shared<f32,bfb>")
                                 : (f64 ? "tridiag_tma_shared<f64,thomas>" : "tridiag_tma_shared<f32,thomas>");
   if (tu.variant == 7 && !CM)  // instrumented instantiation (phase trace)
-    return exact ? launch_shared_tma<R, true, true, false>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name)
-                 : launch_shared_tma<R, false, true, false>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name);
-  return exact ? launch_shared_tma<R, true, false, CM>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name)
-               : launch_shared_tma<R, false, false, CM>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name);
+    return exact ? launch_shared_tma<R, true, true, false>(dl, d, du, X, Xin, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name)
+                 : launch_shared_tma<R, false, true, false>(dl, d, du, X, Xin, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name);
+  return exact ? launch_shared_tma<R, true, false, CM>(dl, d, du, X, Xin, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name)
+               : launch_shared_tma<R, false, false, CM>(dl, d, du, X, Xin, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name);
 }
 
 // level-major operands: dl,d,du [nlev][a_stride], X [nrhs][nlev][x_stride]
 template <typename R>
 int tridiag_tma_shared(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nrhs, int64_t a_stride,
                        int64_t x_stride, cudaStream_t stream) {
-  return run_shared<R, false>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
+  return run_shared<R, false>(exact, dl, d, du, X, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
+}
+// same, out of place: right-hand sides read from B, solutions written to X (same shape and pitch; B is not modified)
+template <typename R>
+int tridiag_tma_shared_oop(bool exact, R* dl, R* d, R* du, const R* B, R* X, int64_t ncol, int nlev, int nrhs,
+                           int64_t a_stride, int64_t x_stride, cudaStream_t stream) {
+  return run_shared<R, false>(exact, dl, d, du, X, B, ncol, nlev, nrhs, a_stride, x_stride, stream);
 }
 // the reference's column-major operands, one right-hand side (f64): dl,d,du [ncol][a_stride], X [ncol][x_stride]
 template <typename R>
 int tridiag_tma_shared_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride,
                           cudaStream_t stream) {
-  return run_shared<R, true>(exact, dl, d, du, X, ncol, nlev, 1, a_stride, x_stride, stream);
+  return run_shared<R, true>(exact, dl, d, du, X, X, ncol, nlev, 1, a_stride, x_stride, stream);
 }
 
 int debug_trace(long long* out, int n) {
@@ -664,6 +673,10 @@ int debug_trace(long long* out, int n) {
 
 template int tridiag_tma_shared<double>(bool, double*, double*, double*, double*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
 template int tridiag_tma_shared<float>(bool, float*, float*, float*, float*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
+template int tridiag_tma_shared_oop<double>(bool, double*, double*, double*, const double*, double*, int64_t, int, int, int64_t, int64_t,
+                                            cudaStream_t);
+template int tridiag_tma_shared_oop<float>(bool, float*, float*, float*, const float*, float*, int64_t, int, int, int64_t, int64_t,
+                                           cudaStream_t);
 template int tridiag_tma_shared_cm<double>(bool, double*, double*, double*, double*, int64_t, int, int64_t, int64_t, cudaStream_t);
 template int tridiag_tma_shared_cm<float>(bool, float*, float*, float*, float*, int64_t, int, int64_t, int64_t, cudaStream_t);
 

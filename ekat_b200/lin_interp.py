@@ -142,3 +142,22 @@ def tridiag_lin_interp(dl, d, du, B, x1, x2, Y2, X=None, ncol=None):
                                  Y2.data_ptr(), X.data_ptr() if X is not None else None, ncol, nlev, km2, nrhs, pitch,
                                  _stream()))
     return Y2
+
+
+def lin_interp_lm(x1, x2, y1, y2, ncol=None):
+    """ekat::LinInterp setup + lin_interp on level-major operands: x1 [km1,pitch], x2 [km2,pitch],
+    y1 [nf,km1,pitch] (or [km1,pitch]), y2 [nf,km2,pitch] (or [km2,pitch]); contiguous, columns fastest."""
+    y13 = y1 if y1.dim() == 3 else y1.unsqueeze(0)
+    y23 = y2 if y2.dim() == 3 else y2.unsqueeze(0)
+    nf, km1, pitch = y13.shape
+    km2 = x2.shape[0]
+    ncol = pitch if ncol is None else ncol
+    if x1.shape != (km1, pitch) or x2.shape != (km2, pitch) or y23.shape != (nf, km2, pitch):
+        raise ValueError("x1 [km1,pitch], x2 [km2,pitch], y1 [nf,km1,pitch], y2 [nf,km2,pitch]")
+    for t in (x1, x2, y13, y23):
+        if not (t.is_cuda and t.is_contiguous() and t.dtype == x1.dtype):
+            raise ValueError("lin_interp_lm needs contiguous CUDA tensors of one dtype (there is no CPU path)")
+    fn = f"ekat_b200_lin_interp_lm_{_SFX[x1.dtype]}"
+    check(fn, getattr(lib(), fn)(x1.data_ptr(), x2.data_ptr(), y13.data_ptr(), y23.data_ptr(), ncol, km1, km2, pitch, nf,
+                                 _stream()))
+    return y2

@@ -151,6 +151,17 @@ int ekat_b200_tridiag_lin_interp_f32(const float* dl, const float* d, const floa
                                      const float* x1, const float* x2, float* Y2, float* X, int64_t ncol,
                                      int nlev, int km2, int nrhs, int64_t pitch, ekat_b200_stream_t stream);
 
+/* LinInterp on LEVEL-MAJOR operands (the tridiagonal kernels' native layout), fused setup + lin_interp for
+ * nfields fields sharing the coordinates (ekat_lin_interp.hpp:13-16: setup once, interpolate many):
+ *   x1: [km1][pitch]   x2: [km2][pitch]   y1: [nfields][km1][pitch]   y2: [nfields][km2][pitch]
+ * Bit-identical to ekat::LinInterp. y2 may alias y1 when km2 == km1. Needs 16-byte aligned x1, y1 and pitch and
+ * km1 <= 256 (one TMA box per 32-column tile): EKAT_B200_ERR_UNSUPPORTED otherwise -- transpose with
+ * ekat_b200_lev_to_col_* and use ekat_b200_lin_interp_* then. */
+int ekat_b200_lin_interp_lm_f64(const double* x1, const double* x2, const double* y1, double* y2, int64_t ncol,
+                                int km1, int km2, int64_t pitch, int nfields, ekat_b200_stream_t stream);
+int ekat_b200_lin_interp_lm_f32(const float* x1, const float* x2, const float* y1, float* y2, int64_t ncol, int km1,
+                                int km2, int64_t pitch, int nfields, ekat_b200_stream_t stream);
+
 /* ------------------------------------------------------------------------
  * Layout marshalling: [ncol][n] <-> [n][pitch] device
  * transposes at copy speed, so callers holding reference-layout views can use

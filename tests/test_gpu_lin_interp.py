@@ -148,3 +148,32 @@ def test_config2_full_size(cuda, port):
         want, _ = port.lin_interp(x1[c0:c0 + 50].cpu().numpy(), x2[c0:c0 + 50].cpu().numpy(), y1[c0:c0 + 50].cpu().numpy(), 72, 128, N)
         assert bits_equal(outs[-1][c0:c0 + 50], want[:, :128])
     assert bits_equal(np.ascontiguousarray(outs[0]), np.ascontiguousarray(outs[1]))
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+def test_level_major_parity_bitwise(cuda, port, dt):
+    """ekat_b200_lin_interp_lm_*: the same interpolation on level-major operands ([level][column], the tridiagonal
+    kernels' native layout), several fields sharing the coordinates, ragged column counts, in place when km2 == km1."""
+    from ekat_b200.lin_interp import lin_interp_lm
+    npdt, tdt = DT[dt]
+    rng = np.random.default_rng(5)
+    for km1, km2, ncol, pad, nf in [(128, 128, 1000, 0, 10), (72, 128, 301, 3, 3), (10, 10, 5, 3, 1), (100, 37, 64, 0, 2),
+                                    (2, 5, 3, 1, 1), (73, 129, 41, 3, 4), (256, 200, 70, 2, 2)]:
+        x1, y1, x2 = synth.lin_interp_inputs(npdt, ncol, km1, km2, 1, col0=3)
+        x2[1, 0] = x1[1, 0] - 0.75
+        x2[1, km2 - 1] = x1[1, km1 - 1] + 1.25
+        m = min(km1, km2)
+        x2[2, :m] = x1[2, :m]
+        x2[0, :km2] = rng.permutation(x2[0, :km2])
+        y1f = np.stack([(f + 1) * y1 - f for f in range(nf)]).astype(npdt)          # [nf, ncol, km1]
+        want, _ = port.lin_interp(x1, x2, y1f, km1, km2, 1)                          # [nf, ncol, km2]
+        lev = lambda a: torch.from_numpy(np.pad(np.ascontiguousarray(np.swapaxes(a, -1, -2)), [(0, 0)] * (a.ndim - 1) + [(0, pad)])).to(cuda)
+        tx1, tx2, ty1 = lev(x1), lev(x2), lev(y1f)
+        ty2 = torch.full((nf, km2, ncol + pad), -777.0, dtype=tdt, device=cuda)
+        lin_interp_lm(tx1, tx2, ty1, ty2, ncol=ncol)
+        got = ty2.cpu().numpy()
+        assert bits_equal(np.ascontiguousarray(got[:, :, :ncol].transpose(0, 2, 1)), want), (km1, km2, ncol, nf)
+        assert (got[:, :, ncol:] == -777.0).all(), "columns beyond ncol must not be written"
+        if km1 == km2:  # in place
+            lin_interp_lm(tx1, tx2, ty1, ty1, ncol=ncol)
+            assert bits_equal(np.ascontiguousarray(ty1.cpu().numpy()[:, :, :ncol].transpose(0, 2, 1)), want)

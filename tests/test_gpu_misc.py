@@ -61,7 +61,7 @@ def test_checksum_and_residual_equal_oracle(cuda, port, dt):
 def test_fused_solve_and_remap(cuda, port, dt):
     """BASELINE config 4 shape (reduced column count): 10-RHS shared-A solve + remap of the 10 solutions."""
     npdt, tdt = DT[dt]
-    for ncol, nlev, km2, nrhs in [(200, 128, 128, 10), (37, 72, 128, 3), (50, 33, 17, 1)]:
+    for ncol, nlev, km2, nrhs in [(200, 128, 128, 10), (37, 72, 128, 3), (50, 33, 17, 1), (4744, 128, 128, 10), (1000, 72, 72, 4)]:
         A, B = port.fill_tridiag(npdt, ncol, nlev, 1, nrhs, col0=4)
         x1, _, x2 = synth.lin_interp_inputs(npdt, ncol, nlev, km2, 1, col0=4)
         Xref = port.tridiag("thomas", A.copy(), B.copy())                       # [ncol,nlev,nrhs]
@@ -79,7 +79,7 @@ def test_fused_solve_and_remap(cuda, port, dt):
         # and it equals the unfused GPU path (thomas, then LinInterp on the transposed solution) to tolerance
         Y2b = torch.zeros_like(Y2)
         tridiag_lin_interp(dl, d, du, Bd, x1d, x2d, Y2b, None)
-        assert torch.equal(Y2, Y2b)
+        assert rel_diff(Y2.cpu().numpy(), Y2b.cpu().numpy()) <= 10 * tol(npdt)  # (may take the one-kernel path: other thomas rounding)
 
 
 @pytest.mark.parametrize("dt", ["f64", "f32"])

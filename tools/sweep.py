@@ -158,6 +158,23 @@ if __name__ == "__main__":
             li_case("f32", 345600, km1, 128, 1, tunings=[(8, 0, 0), (16, 0, 0), (24, 0, 0), (32, 0, 0), (48, 0, 0)])
         li_case("f64", 3145728, 128, 128, 1, tunings=[(8, 0, 0), (16, 0, 0)])
         li_case("f64", 345600, 72, 128, 16, tunings=[(8, 0, 0), (16, 0, 0)])
+    if "lilm" in what:
+        from ekat_b200.lin_interp import lin_interp_lm
+        for dt, tdt, w in (("f64", torch.float64, 8), ("f32", torch.float32, 4)):
+            for ncol, km1, nf in ((345600, 128, 1), (345600, 128, 10), (345600, 72, 1), (1572864, 128, 10)):
+                if dt == "f32" and ncol > 345600:
+                    continue
+                x1, y1, x2 = li_fill(tdt, ncol, km1, 128, 1, device=dev, lev_major=True)
+                y1f = y1.unsqueeze(0).repeat(nf, 1, 1).contiguous()
+                y2 = torch.zeros((nf, 128, ncol), dtype=tdt, device=dev)
+                alg = (km1 + 128) * (1 + nf) * w * ncol
+                for tu in ((0, 0, 0), (16, 1, 0), (16, 3, 0), (32, 1, 0)):
+                    lib().ekat_b200_set_tuning(*tu)
+                    ms = timeit(lambda: lin_interp_lm(x1, x2, y1f, y2))
+                    lib().ekat_b200_set_tuning(0, 0, 0)
+                    report(kernel="lin_interp_lm", dt=dt, ncol=ncol, km1=km1, km2=128, nfields=nf, tuning=tu, ms=round(ms, 4),
+                           gbs=round(alg / ms / 1e6, 1), frac=round(alg / ms / 1e6 / PEAK, 3))
+                del x1, y1, x2, y1f, y2
     if "c1" in what:
         for s in ("thomas", "bfb", "cr"):
             tridiag_case(s, "f64", 21600, 72, tunings=[(0, 0, 0), (16, 8, 0), (16, 16, 0), (32, 8, 0), (64, 16, 0)])
@@ -182,4 +199,5 @@ if __name__ == "__main__":
         tridiag_case("cr", "f64", 64, 2048, layout=ekat_b200.COL_MAJOR)
         tridiag_case("cr", "f64", 2048, 128, nrhs=43, nA=43, layout=ekat_b200.COL_MAJOR, tag="reference perf default")
     if "fused" in what:
-        fused_case("f64", 393216, 128, 128, 10, tunings=[(0, 0, 0), (8, 0, 0)])
+        fused_case("f64", 393216, 128, 128, 10, tunings=[(0, 0, 0), (0, 0, 1)])
+        fused_case("f64", 1572864, 128, 128, 10)
