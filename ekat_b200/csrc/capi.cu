@@ -19,6 +19,8 @@ template <typename R>
 int tridiag_tma_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride,
                    cudaStream_t stream);
 template <typename R>
+int tridiag_cr_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride, cudaStream_t stream);
+template <typename R>
 int tridiag_tma_shared_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride,
                           cudaStream_t stream);
 template <typename R>
@@ -87,7 +89,13 @@ static int tridiag_entry(int solver, R* dl, R* d, R* du, R* X, int64_t ncol, int
     if (a_stride < (int64_t)nlev * nA || x_stride < (int64_t)nlev * nrhs) return EKAT_B200_ERR_INVALID;
   }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (solver == SOLVER_CR) return tridiag_tile<R>(2, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, layout, flags, st);
+  if (solver == SOLVER_CR) {
+    if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && nA == 1 && nrhs == 1 && !flags && tuning().variant == 0) {
+      const int rc = tridiag_cr_tma<R>(dl, d, du, X, ncol, nlev, a_stride, x_stride, st);  // many columns (tridiag_cr_tma.cu)
+      if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+    }
+    return tridiag_tile<R>(2, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, layout, flags, st);
+  }
   if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && tuning().variant != 2)
     return tridiag_levmajor<R>(solver == SOLVER_BFB, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, flags, st);
   if (layout == EKAT_B200_LAYOUT_COL_MAJOR && nA == 1 && nrhs == 1 && !flags && (tuning().variant == 0 || tuning().variant == 4)) {

@@ -248,3 +248,18 @@ def test_shared_matrix_persistent_many_items(cuda, port, dt, solver):
         assert lib().ekat_b200_last_kernel().decode().startswith("tridiag_tma_shared"), lib().ekat_b200_last_kernel()
         check(solver, got, want, npdt, (dt, nrow, nrhs, ncol))
         assert bits_equal(Aout, A)
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+def test_cr_many_columns_bit_exact(cuda, port, dt):
+    """Cyclic reduction at column counts that take the TMA tile kernel (tridiag_cr_tma.cu): bit-identical to the
+    reference's CR for power-of-two, odd and tiny level counts, ragged last tile."""
+    npdt, _ = DT[dt]
+    from ekat_b200._lib import lib
+    for nrow, ncol in [(128, 9472 + 5), (72, 9600), (43, 9473), (129, 9480), (5, 9999), (2, 9500), (1, 9476), (3, 9481), (65, 9700)]:
+        A, B = port.fill_tridiag(npdt, ncol, nrow, 1, 1, col0=2)
+        want = port.tridiag("cr", A.copy(), B.copy())
+        got, Aout = run_gpu("cr", A, B, ekat_b200.LEV_MAJOR, cuda, pad=(-ncol) % 4)
+        assert lib().ekat_b200_last_kernel().decode().startswith("tridiag_cr_tma"), lib().ekat_b200_last_kernel()
+        assert bits_equal(got, want), (dt, nrow, ncol, rel_diff(want, got))
+        assert bits_equal(Aout, A)
