@@ -344,7 +344,9 @@ def run_extras(torch, dev, peak):
     tri("config 3, thomas, reference (column-major) layout", "thomas", 345600, 128, 1, 1, CMJ)
     tri("config 3, bfb, reference (column-major) layout", "bfb", 345600, 128, 1, 1, CMJ)
     tri("config 3, thomas f32, level-major", "thomas", 345600, 128, 1, 1, LM, torch.float32)
-    tri("config 3, cr, level-major", "cr", 345600, 128, 1, 1, LM)
+    tri("config 3, cr (bit-exact), level-major", "cr", 345600, 128, 1, 1, LM)
+    tri("config 3, thomas, level-major", "thomas", 345600, 128, 1, 1, LM)
+    tri("config 3, bfb (bit-exact), level-major", "bfb", 345600, 128, 1, 1, LM)
     tri("config 1, thomas, 21,600 x 72 (fits L2; launch-latency bound)", "thomas", 21600, 72, 1, 1, LM)
     for km1, N, label in ((72, 16, "config 2, LinInterp 72->128, Pack<double,16> pitch"), (72, 1, "config 2, LinInterp 72->128, scalar pitch")):
         ncol = 345600
@@ -355,6 +357,17 @@ def run_extras(torch, dev, peak):
         alg = (2 * km1 + 2 * 128) * 8 * ncol
         out.append({"case": label + f" ({ncol} columns)", "kernel": lib().ekat_b200_last_kernel().decode(), "ms": ms,
                     "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak, "col_lev_per_s": ncol * 128 / ms * 1e3})
+    # config 4 whole: 10-rhs solve + remap of the 10 solutions (persistent TMA solve, then level-major LinInterp)
+    from ekat_b200.lin_interp import tridiag_lin_interp
+    ncol, nrhs = 1572864, 10
+    dl, d, du, Bm = T.fill(torch.float64, ncol, 128, 1, nrhs, device=dev)
+    x1, _, x2 = li_fill(torch.float64, ncol, 128, 128, 1, device=dev, lev_major=True)
+    Y2 = torch.zeros((nrhs, 128, ncol), dtype=torch.float64, device=dev)
+    ms = timed(lambda: tridiag_lin_interp(dl[0], d[0], du[0], Bm, x1, x2, Y2))
+    alg = (3 + nrhs + 2 + nrhs) * 128 * 8 * ncol
+    out.append({"case": "config 4, 10-rhs thomas + LinInterp 128->128 of the 10 solutions (25,600 B/column algorithmic)",
+                "kernel": "tridiag_tma_shared<f64,thomas> + " + lib().ekat_b200_last_kernel().decode(), "ms": ms,
+                "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak, "col_lev_per_s": ncol * 128 / ms * 1e3})
     return out
 
 
