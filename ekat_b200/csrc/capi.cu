@@ -98,7 +98,7 @@ static int tridiag_entry(int solver, R* dl, R* d, R* du, R* X, int64_t ncol, int
   }
   if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && tuning().variant != 2)
     return tridiag_levmajor<R>(solver == SOLVER_BFB, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, flags, st);
-  if (layout == EKAT_B200_LAYOUT_COL_MAJOR && nA == 1 && nrhs == 1 && !flags && (tuning().variant == 0 || tuning().variant == 4)) {
+  if (layout == EKAT_B200_LAYOUT_COL_MAJOR && nA == 1 && nrhs == 1 && !flags && (tuning().variant == 0 || (tuning().variant >= 4 && tuning().variant <= 6) || tuning().variant == 10 || tuning().variant == 11)) {
     // reference layout, one right-hand side: the TMA kernel reads the columns where they lie (tridiag_tma.cu)
     if (solver == SOLVER_THOMAS && tuning().variant == 0) {  // f64: factor and solve chains on different warps
       const int rc = tridiag_tma_shared_cm<R>(false, dl, d, du, X, ncol, nlev, a_stride, x_stride, st);

@@ -357,8 +357,15 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
 // three. The top chunk is never spilled: the back-substitution starts from it where it lies.
 // Ring stage = [dl | du | x], LB levels each. Use u < nch: forward chunk u. Use u >= nch: (du, x') of chunk
 // 2*nch-2-u for the back-substitution. A stage is refilled once the tensor store that reads it has done so.
-template <typename R, int CPT, int NS, int LBT, bool CM>
-__global__ void __launch_bounds__(32)
+// IO = 0: one warp per tile does everything. IO = 1: a second warp (one thread of it) issues every copy.
+// IO = 2: as 1, and TWO sweeping warps take the chunks of the tile in turn: the dependent chain of a chunk is only
+// ~45% of the time a single warp spends on it (ncu: the rest is waiting for the copy, 32 LDS, 16 STS, the proxy fence,
+// the arrival, index arithmetic), so while one warp runs the chain of chunk k the other one stores the results of
+// chunk k-1 and stages the operands of chunk k+1 in registers. The chain state (d', x', du of the previous level;
+// x of the level above on the way back) crosses in shared memory under a pair of named barriers (bar.arrive by the
+// warp that finished, bar.sync by the warp that continues).
+template <typename R, int CPT, int NS, int LBT, bool CM, int IO>
+__global__ void __launch_bounds__(IO == 2 ? 96 : IO ? 64 : 32)
 k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
                     const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mx, R* __restrict__ X,
                     int64_t ncol, int nlev, int64_t x_stride, int pd) {
@@ -366,24 +373,33 @@ k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_consta
   constexpr int LB = LBT, W = 32 * CPT, CH = LB * 32;
   constexpr unsigned CHUNK_BYTES = LB * W * sizeof(R);
   extern __shared__ __align__(1024) unsigned char smem_raw[];
-  const int lane = threadIdx.x;
+  constexpr int NCW = IO == 2 ? 2 : 1;  // sweeping warps
+  constexpr bool PP = IO == 2;
+  const int lane = threadIdx.x & 31, cw = threadIdx.x >> 5;
+  const bool io_warp = IO && cw == NCW;
   const int nfull = nlev / LB, ntail = nlev - nfull * LB, nch = nfull + (ntail ? 1 : 0);
   const int NU = 2 * nch - 1;  // ring uses
 
   uint64_t* rbar = reinterpret_cast<uint64_t*>(smem_raw);  // [NS] ring stage landed
-  uint64_t* pbar = rbar + NS;                              // [nch] pivot-plane chunk landed
+  uint64_t* dbar = rbar + NS;                              // [2][NS] IO: the forward / backward sweep is done with the stage
+  uint64_t* pbar = dbar + 2 * NS;                          // [nch] pivot-plane chunk landed
   constexpr size_t AL = CM ? 1024 : 128;  // swizzled chunks sit on 1 KB boundaries
-  const size_t off = ((size_t)(NS + nch) * 8 + AL - 1) & ~(AL - 1);
+  const size_t hs_off = ((size_t)(3 * NS + nch) * 8 + 15) & ~(size_t)15;
+  V* HS = reinterpret_cast<V*>(smem_raw + hs_off);  // PP: chain state handed from one sweeping warp to the other [3][32]
+  const size_t off = (hs_off + (PP ? 3 * 32 * sizeof(V) : 0) + AL - 1) & ~(AL - 1);
   V* P0 = reinterpret_cast<V*>(smem_raw + off);  // d -> d'
   V* RG = P0 + (size_t)nch * CH;                 // [NS][3][LB][32]
+  auto hand_wait = [&]() { asm volatile("bar.sync %0, 64;" ::"r"(1 + cw) : "memory"); };       // state for this warp is there
+  auto hand_over = [&]() { asm volatile("bar.arrive %0, 64;" ::"r"(2 - cw) : "memory"); };     // state for the other warp is there
 
   const int c0 = blockIdx.x * W;
   const int row0 = blockIdx.y * nlev;
-  if (lane == 0) {
-    for (int s = 0; s < NS + nch; ++s) mbar_init(&rbar[s], 1);
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 3 * NS + nch; ++s) mbar_init(&rbar[s], 1);
     fence_mbar_init();
   }
-  __syncwarp();
+  if (IO) __syncthreads();
+  else __syncwarp();
   const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
 
   auto load_chunk = [&](void* dst, const CUtensorMap* m, int k, uint64_t* bar, uint64_t pol) {
@@ -415,7 +431,49 @@ k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_consta
     load_chunk(P0 + (size_t)k * CH, &md, k, &pbar[k], pol_stream);
   };
   auto ld = [&](const V* chunk, int u) { return t_ld<R, CPT, LB, CM>(chunk, u, lane); };
-  if (lane == 0) {
+  if (io_warp) {
+    // ------------------------------------------------------------ io warp (IO): one thread issues every copy.
+    // A tensor copy costs its issuing thread ~130 cycles (measured); five per forward chunk and three per backward
+    // chunk on the sweeping warp were a third of a tile's time. Here the sweeping warp only arrives on dbar[stage]
+    // when a chunk's results are in shared memory (fenced for the async proxy); this thread stores the chunk, waits
+    // until the store has read it, and refills the stage with the use NS ahead.
+    if (lane != 0) return;
+    for (int k = 0; k < pd && k < nch; ++k) issue_plane(k);
+    for (int u = 0; u < NS && u < nch; ++u) issue_use(u);
+    // Arrivals of the forward and of the backward sweep go to separate barriers: the top chunk's stage is finished
+    // twice in a row (forward, then backward) and two arrivals on one barrier could flip its phase twice unseen.
+    unsigned dph = 0;  // phase bit per barrier
+    auto wait_done = [&](int s) {
+      mbar_wait(&dbar[s], (dph >> s) & 1u);
+      dph ^= 1u << s;
+    };
+    for (int k = 0; k < nch; ++k) {
+      const int s = k % NS;
+      wait_done(s);
+      if (k + pd < nch) issue_plane(k + pd);
+      if (k < nch - 1) {  // the top chunk stays where it is
+        store_chunk(k, RG + (size_t)s * 3 * CH + 2 * CH, pol_keep);
+        if (k + NS < nch) {
+          tma_store_wait_read<0>();
+          issue_use(k + NS);
+        }
+      }
+    }
+    tma_store_wait_all<0>();  // turn-around: every x' must have reached L2 before it is read back
+    for (int u = nch; u < NU && u < nch + NS - 1; ++u) issue_use(u);
+    for (int jb = 0; jb < nch; ++jb) {
+      const int k = nch - 1 - jb, u0 = nch - 1 + jb, s = u0 % NS;
+      wait_done(NS + s);
+      if (CM || k != nfull) store_chunk(k, RG + (size_t)s * 3 * CH + 2 * CH, pol_stream);
+      if (u0 + NS < NU) {
+        tma_store_wait_read<0>();
+        issue_use(u0 + NS);
+      }
+    }
+    tma_store_wait_read<0>();  // shared memory must outlive the stores' reads
+    return;
+  }
+  if (!IO && lane == 0) {
     for (int k = 0; k < pd && k < nch; ++k) issue_plane(k);
     for (int u = 0; u < NS && u < nch; ++u) issue_use(u);
   }
@@ -428,7 +486,7 @@ k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_consta
     xprev[j] = (R)0;
     uprev[j] = (R)0;
   }
-  for (int k = 0; k < nch; ++k) {
+  for (int k = PP ? cw : 0; k < nch; k += NCW) {
     const int s = k % NS;
     mbar_wait(&rbar[s], (unsigned)(k / NS) & 1u);
     mbar_wait(&pbar[k], 0u);
@@ -441,6 +499,16 @@ k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_consta
       c[u] = ld(st + CH, u);
       x[u] = ld(st + 2 * CH, u);
       b[u] = ld(p0, u);
+    }
+    if (PP && k > 0) {  // the other warp has finished chunk k-1: take over the chain
+      hand_wait();
+      const V h0 = HS[lane], h1 = HS[32 + lane], h2 = HS[64 + lane];
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) {
+        dprev[j] = h0.v[j];
+        xprev[j] = h1.v[j];
+        uprev[j] = h2.v[j];
+      }
     }
     R sd[CPT], sx[CPT], su[CPT];
 #pragma unroll
@@ -460,15 +528,31 @@ k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_consta
       }
       bfb_fwd_chunk<R, CPT, LB, true>(a, b, c, x, o0, o1, dprev, xprev, uprev, k == 0, bad);
     }
+    if (PP && k < nch - 1) {  // hand the chain on before anything else: the other warp's chunk starts now
+      V h0, h1, h2;
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) {
+        h0.v[j] = dprev[j];
+        h1.v[j] = xprev[j];
+        h2.v[j] = uprev[j];
+      }
+      HS[lane] = h0;
+      HS[32 + lane] = h1;
+      HS[64 + lane] = h2;
+      hand_over();
+    }
 #pragma unroll
     for (int u = 0; u < LB; ++u) {
       t_st<R, CPT, LB, CM>(p0, u, lane, o0[u]);
       t_st<R, CPT, LB, CM>(st + 2 * CH, u, lane, o1[u]);
     }
+    if (PP && k == nch - 1) hand_over();  // turn-around: the top chunk's d' and x' must be in shared memory first
     const bool spill = k < nch - 1;  // the top chunk stays where it is
     if (spill) fence_proxy_async();
     __syncwarp();
-    if (lane == 0) {
+    if (IO) {
+      if (lane == 0) mbar_arrive(&dbar[s]);
+    } else if (lane == 0) {
       if (spill) store_chunk(k, st + 2 * CH, pol_keep);
       if (k >= 1 && k - 1 + NS < nch) {  // the stage of chunk k-1 is free once its store has read it
         if (spill) tma_store_wait_read<1>();
@@ -479,7 +563,7 @@ k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_consta
     }
   }
   // turn-around: every x' must have reached L2 before it is read back
-  if (lane == 0) {
+  if (!IO && lane == 0) {
     tma_store_wait_all<0>();
     for (int u = nch; u < NU && u < nch + NS - 1; ++u) issue_use(u);
   }
@@ -488,7 +572,17 @@ k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_consta
   R xv[CPT];
 #pragma unroll
   for (int j = 0; j < CPT; ++j) xv[j] = (R)0;
-  for (int jb = 0; jb < nch; ++jb) {
+  // PP: the chunks keep alternating between the two warps across the turn-around (step nch + jb belongs to warp
+  // (nch + jb) % 2). What a step reads was written by the other warp -- the pivots of chunk k always, x' of the top
+  // chunk -- before a hand_over that precedes this step's hand_wait; only for jb <= 1 is that hand_over the one
+  // this very step waits for, so those two steps wait before they load and all later ones load first.
+  auto take_x = [&]() {
+    hand_wait();
+    const V h0 = HS[lane];
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) xv[j] = h0.v[j];
+  };
+  for (int jb = PP ? ((nch + cw) & 1) : 0; jb < nch; jb += NCW) {
     const int k = nch - 1 - jb, u0 = nch - 1 + jb, s = u0 % NS;
     if (jb > 0) mbar_wait(&rbar[s], (unsigned)(u0 / NS) & 1u);
     V* st = RG + (size_t)s * 3 * CH;
@@ -496,6 +590,8 @@ k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_consta
     V* xs = st + 2 * CH;
     const V* q0p = P0 + (size_t)k * CH;
     bool stored = true;
+    if (PP && jb == 0) hand_wait();  // xv stays 0
+    if (PP && jb == 1) take_x();
     if (k == nfull) {
       // partial top chunk (ntail levels)
       const int64_t col = (int64_t)c0 + lane * CPT;
@@ -534,6 +630,7 @@ k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_consta
 #pragma unroll
         for (int j = 0; j < CPT; ++j) ui[LB - 1].v[j] = (R)0;
       }
+      if (PP && jb > 1) take_x();
       R sxv[CPT];
       V ys[LB];
 #pragma unroll
@@ -549,12 +646,28 @@ k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_consta
         for (int u = 0; u < LB; ++u) y[u] = ys[u];
         bfb_bwd_chunk<R, CPT, LB, true>(y, m0, ui, xv, bad);
       }
+      if (PP && jb < nch - 1) {
+        V h0;
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) h0.v[j] = xv[j];
+        HS[lane] = h0;
+        hand_over();
+      }
 #pragma unroll
       for (int u = 0; u < LB; ++u) t_st<R, CPT, LB, CM>(xs, u, lane, y[u]);
       fence_proxy_async();  // generic-proxy writes of this chunk -> visible to the TMA store
     }
+    if (PP && k == nfull && jb < nch - 1) {  // after the ragged top chunk
+      V h0;
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) h0.v[j] = xv[j];
+      HS[lane] = h0;
+      hand_over();
+    }
     __syncwarp();
-    if (lane == 0) {
+    if (IO) {
+      if (lane == 0) mbar_arrive(&dbar[NS + s]);
+    } else if (lane == 0) {
       if (stored) store_chunk(k, xs, pol_stream);
       if (jb >= 1 && u0 - 1 + NS < NU) {  // the stage of the previous step is free once its store has read it
         if (stored) tma_store_wait_read<1>();
@@ -563,23 +676,10 @@ k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_consta
       }
     }
   }
-  if (lane == 0) tma_store_wait_read<0>();  // shared memory must outlive the stores' reads
+  if (!IO && lane == 0) tma_store_wait_read<0>();  // shared memory must outlive the stores' reads
 }
 
 // ------------------------------------------------------------------------------------------- host side
-// Chunk length and renormalisation interval per layout. Column-major rows are 64 bytes swizzled (f64) or 48 bytes (f32), see t_ld.
-template <typename R, bool CM>
-struct TmaGeom {
-  static constexpr int LB = kLB, RN = TmaCfg<R>::RN;
-};
-template <>
-struct TmaGeom<double, true> {
-  static constexpr int LB = 8, RN = 8;  // 64-byte rows, swizzled
-};
-template <>
-struct TmaGeom<float, true> {
-  static constexpr int LB = 12, RN = 2;
-};
 
 template <typename R, bool EXACT, int NS, bool CM>
 static int launch_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
@@ -606,7 +706,7 @@ static int launch_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat
   return check_cuda(cudaGetLastError());
 }
 
-template <typename R, int NS, bool CM>
+template <typename R, int NS, bool CM, int IO>
 static int launch_spill(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
                         int pd, size_t smem, cudaStream_t stream, const char* name) {
   constexpr int CPT = TmaCfg<R>::CPT, LB = TmaGeom<R, CM>::LB, W = 32 * CPT;
@@ -622,11 +722,11 @@ static int launch_spill(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nm
          make_tensor_map_2d<R>(&mdu, du, ncol, rows, a_stride, W, LB, 0) && make_tensor_map_2d<R>(&mx, X, ncol, rows, x_stride, W, LB, 0);
   }
   if (!ok) return EKAT_B200_ERR_UNSUPPORTED;
-  auto k = k_tridiag_bfb_spill<R, CPT, NS, LB, CM>;
+  auto k = k_tridiag_bfb_spill<R, CPT, NS, LB, CM, IO>;
   int rc = allow_smem(k, smem);
   if (rc) return rc;
   dim3 grid((unsigned)((ncol + W - 1) / W), (unsigned)nmat);
-  k<<<grid, 32, smem, stream>>>(mdl, md, mdu, mx, X, ncol, nlev, x_stride, pd);
+  k<<<grid, IO == 2 ? 96 : IO ? 64 : 32, smem, stream>>>(mdl, md, mdu, mx, X, ncol, nlev, x_stride, pd);
   note_launch(name);
   return check_cuda(cudaGetLastError());
 }
@@ -646,11 +746,19 @@ static int run_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev,
   const int nch = (nlev + LB - 1) / LB;
   const size_t chunk = (size_t)LB * W * sizeof(R);
   const bool f64 = sizeof(R) == 8;
+  // bfb from 96 levels up: input-only copy ring, two sweeping warps (tridiag_bfb_stream.cu). Shorter columns leave room
+  // for five or more tiles of the one-sweeping-warp kernel below, which then wins (measured at 72 levels: 79% against
+  // 71%; at 96: 74% against 76%; at 128: 66% against 75-82%); so it does for column-major f32 (12-level chunks).
+  if (exact && (tu.variant == 0 || tu.variant == 6) && (nlev >= 96 || tu.variant == 6) && !(CM && sizeof(R) == 4)) {
+    const int rc = tridiag_bfb_stream<R, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, stream);
+    if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+  }
   if (exact && tu.variant != 4) {
     // bfb: pivots on chip, x' through L2 (k_tridiag_bfb_spill): as many tiles per SM as a 3- or 4-stage ring allows
     const size_t al = CM ? 1024 : 128;
     auto smem_for = [&](int stages) {
-      return (((size_t)(stages + nch) * 8 + al - 1) & ~(al - 1)) + (size_t)nch * chunk + (size_t)stages * 3 * chunk;
+      const size_t hs = (((size_t)(3 * stages + nch) * 8 + 15) & ~(size_t)15) + 3 * 32 * sizeof(R) * CPT;  // barriers + hand-over state
+      return ((hs + al - 1) & ~(al - 1)) + (size_t)nch * chunk + (size_t)stages * 3 * chunk;
     };
     auto tiles = [&](int stages) { return (int)((kMaxSmemPerCta + 1024) / (smem_for(stages) + 1024)); };
     // three stages (two chunks in flight behind the one being swept) are what the re-loads of the back-substitution
@@ -663,9 +771,13 @@ static int run_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev,
       const int pd = tu.prefetch > 0 ? tu.prefetch : 3;
       const char* name = CM ? (f64 ? "tridiag_bfb_spill_cm<f64>" : "tridiag_bfb_spill_cm<f32>")
                             : (f64 ? "tridiag_bfb_spill<f64>" : "tridiag_bfb_spill<f32>");
-      return ns == 4   ? launch_spill<R, 4, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem_for(4), stream, name)
-             : ns == 3 ? launch_spill<R, 3, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem_for(3), stream, name)
-                       : launch_spill<R, 2, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem_for(2), stream, name);
+      // variant 5: the single-warp form (the sweeping warp issues its own copies), variant 11: two sweeping warps + io
+      // warp; kept for A/B measurements. Default: one sweeping warp + io warp.
+#define EKB_SPILL(NS_, IO_) launch_spill<R, NS_, CM, IO_>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem_for(NS_), stream, name)
+      if (tu.variant == 5) return ns == 4 ? EKB_SPILL(4, 0) : ns == 3 ? EKB_SPILL(3, 0) : EKB_SPILL(2, 0);
+      if (tu.variant == 11) return ns == 4 ? EKB_SPILL(4, 2) : ns == 3 ? EKB_SPILL(3, 2) : EKB_SPILL(2, 2);
+      return ns == 4 ? EKB_SPILL(4, 1) : ns == 3 ? EKB_SPILL(3, 1) : EKB_SPILL(2, 1);
+#undef EKB_SPILL
     }
   }
   const size_t bars = ((size_t)(12 + nch) * 8 + 1023) & ~(size_t)1023;

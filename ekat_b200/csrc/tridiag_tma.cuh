@@ -125,4 +125,25 @@ __device__ __forceinline__ void bfb_bwd_chunk(Vec<R, CPT> (&y)[LB], const Vec<R,
 }
 
 
+// Chunk length and renormalisation interval per layout. Column-major rows are 64 bytes swizzled (f64) or 48 bytes (f32), see t_ld.
+template <typename R, bool CM>
+struct TmaGeom {
+  static constexpr int LB = kLB, RN = TmaCfg<R>::RN;
+};
+template <>
+struct TmaGeom<double, true> {
+  static constexpr int LB = 8, RN = 8;  // 64-byte rows, swizzled
+};
+template <>
+struct TmaGeom<float, true> {
+  static constexpr int LB = 12, RN = 2;
+};
+
+// bfb, one matrix and one right-hand side per column, input-only copy ring (tridiag_bfb_stream.cu). Level-major
+// operands [nmat][nlev][stride] (CM = false) or the reference's column-major [ncol][stride] (CM = true, nmat == 1).
+// Returns EKAT_B200_ERR_UNSUPPORTED when a tile does not fit on chip.
+template <typename R, bool CM>
+int tridiag_bfb_stream(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
+                       cudaStream_t stream);
+
 }  // namespace ekb

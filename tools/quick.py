@@ -1,7 +1,9 @@
 import sys; sys.path.insert(0,"tools"); sys.path.insert(0,".")
-import sweep
-for dt in ("f64","f32"):
-    sweep.tridiag_case("bfb", dt, 345600, 128, tunings=[(0,0,0),(2,3,0),(4,3,0),(4,6,0)])
-sweep.tridiag_case("bfb","f64",3145728,128)
-sweep.tridiag_case("bfb","f64",21600,72, tunings=[(0,0,0),(2,3,0),(4,3,0)])
-sweep.tridiag_case("thomas","f64",345600,128)
+import sweep, ekat_b200
+V=[(0,0,0),(0,0,10),(0,0,11)]
+for nlev in (32,64,72,96,128,160,256):
+    sweep.tridiag_case("bfb","f64",345600*128//nlev,nlev, tunings=V)
+for nlev in (72,128,256):
+    sweep.tridiag_case("bfb","f32",345600*128//nlev,nlev, tunings=V)
+    sweep.tridiag_case("bfb","f64",345600*128//nlev,nlev, layout=ekat_b200.COL_MAJOR, tunings=V)
+    sweep.tridiag_case("bfb","f32",345600*128//nlev,nlev, layout=ekat_b200.COL_MAJOR, tunings=V)
