@@ -143,6 +143,26 @@ class CpuOracle:
             _int(packn), _p(x1), _p(x2), _p(y1f), _p(y2), _p(indx), _i64(ncol), _int(km1), _int(km2), _int(nfields))
 
 
+    # ---- ReductionUtils ------------------------------------------------
+    def view_reduction(self, x, begin, end, packn=0):
+        """Per-column sum over the scalar range [begin, end) of x [ncol, pitch].
+        packn = 0: Serialize = true (in order); packn = N >= 1: the reference's packed order for Pack<Real,N>."""
+        x = np.ascontiguousarray(x)
+        ncol, pitch = x.shape
+        out = np.zeros(ncol, x.dtype)
+        s = _sfx(x.dtype)
+        if self.kind == "port":
+            rc = getattr(self.lib, "ekat_oracle_view_reduction_" + s)(
+                _p(x), _p(out), _i64(ncol), _int(begin), _int(end), _i64(pitch), _int(packn))
+        else:
+            rc = getattr(self.lib, "ekat_ref_view_reduction_" + s)(
+                _int(max(packn, 1)), _int(1 if packn == 0 else 0), _p(x), _p(out), _i64(ncol), _int(begin), _int(end),
+                _i64(pitch))
+        if rc != 0:
+            raise ValueError(f"{self.kind} oracle view_reduction rc={rc}")
+        return out
+
+
 _cache = {}
 
 

@@ -7,6 +7,7 @@
 // No reference source is copied here: this file only *calls*
 //   ekat::tridiag::{thomas,cr,bfb}       (src/algorithm/ekat_tridiag.hpp:323-678)
 //   ekat::LinInterp::{setup,lin_interp}  (src/algorithm/ekat_lin_interp.hpp:69-126)
+//   ekat::impl::view_reduction<Serialize> (src/algorithm/ekat_reduction_utils.hpp:67-144)
 //   ekat::test::fill_tridiag_matrix / fill_data_matrix / matvec
 //                                        (tests/algorithm/tridiag_tests.hpp:11-88)
 // through the same batch idiom as the reference's own drivers
@@ -37,6 +38,7 @@
 #include "ekat_lin_interp.hpp"
 #undef private
 #include "ekat_tridiag.hpp"
+#include "ekat_reduction_utils.hpp"
 #include "tridiag_tests.hpp"
 
 namespace {
@@ -203,7 +205,43 @@ int lin_interp(int packn, const S* x1, const S* x2, const S* y1, S* y2, int* ind
 
 }  // namespace
 
+namespace {
+// view_reduction for every column: in [ncol][pitch] scalars = [ncol][pitch/N] packs (pitch % N == 0), out [ncol];
+// called as the reference's test calls it (tests/algorithm/reduction_tests.cpp:117-126), the view as provider.
+template <class S, int N, bool Serialize>
+int view_reduction_n(const S* in, S* out, int64_t ncol, int begin, int end, int64_t pitch) {
+  using P = ekat::Pack<S, N>;
+  if (pitch % N) return -3;
+  Kokkos::parallel_for(Policy((int)ncol, 1), [&](const Member& team) {
+    const int c = team.league_rank();
+    V1<const P> row(reinterpret_cast<const P*>(in + (size_t)c * pitch), pitch / N);
+    out[c] = ekat::impl::view_reduction<Serialize>(team, begin, end, row);
+  });
+  return 0;
+}
+template <class S>
+int view_reduction(int packn, int serialize, const S* in, S* out, int64_t ncol, int begin, int end, int64_t pitch) {
+#define EKAT_REF_VR(N_) \
+  case N_: return serialize ? view_reduction_n<S, N_, true>(in, out, ncol, begin, end, pitch) \
+                            : view_reduction_n<S, N_, false>(in, out, ncol, begin, end, pitch);
+  switch (packn) {
+    EKAT_REF_VR(1) EKAT_REF_VR(2) EKAT_REF_VR(4) EKAT_REF_VR(8) EKAT_REF_VR(16)
+    default: return -4;
+  }
+#undef EKAT_REF_VR
+}
+
+}  // namespace
+
 extern "C" {
+int ekat_ref_view_reduction_f64(int packn, int serialize, const double* in, double* out, int64_t ncol, int begin, int end,
+                                int64_t pitch) {
+  return view_reduction<double>(packn, serialize, in, out, ncol, begin, end, pitch);
+}
+int ekat_ref_view_reduction_f32(int packn, int serialize, const float* in, float* out, int64_t ncol, int begin, int end,
+                                int64_t pitch) {
+  return view_reduction<float>(packn, serialize, in, out, ncol, begin, end, pitch);
+}
 
 int ekat_ref_tridiag_f64(int solver, double* A, double* X, int64_t ncol, int nrow, int nA, int nrhs) {
   return tridiag<double>(solver, A, X, ncol, nrow, nA, nrhs);

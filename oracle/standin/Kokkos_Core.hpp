@@ -289,6 +289,7 @@ class RangePolicy {
   long m_b, m_e;
 };
 
+template <class T> struct reduction_identity;
 namespace standin_impl {
 struct PerTeamTag {};
 struct RangeBoundary { int begin, end; };
@@ -307,6 +308,14 @@ inline standin_impl::RangeBoundary ThreadVectorRange(const standin_impl::TeamMem
 template <class F>
 KOKKOS_FORCEINLINE_FUNCTION void parallel_for(const standin_impl::RangeBoundary& r, const F& f) {
   for (int i = r.begin; i < r.end; ++i) f(i);
+}
+// Team-level reduction of a 1-thread team: the thread's own accumulation, in index order, starting from the
+// identity (what Kokkos::parallel_reduce(TeamThreadRange) gives a team of one).
+template <class F, class T>
+KOKKOS_FORCEINLINE_FUNCTION void parallel_reduce(const standin_impl::RangeBoundary& r, const F& f, T& result) {
+  T acc = reduction_identity<T>::sum();
+  for (int i = r.begin; i < r.end; ++i) f(i, acc);
+  result = acc;
 }
 // League loop: one 1-thread team per league entry, distributed over OpenMP
 // threads exactly as Kokkos::OpenMP distributes TeamPolicy(n, 1).
