@@ -5,6 +5,7 @@ include/ekat_b200/ekat_b200.h (libekat_b200.so, hand-written CUDA):
 
   ekat_b200.tridiag.thomas / bfb / cr      <- ekat::tridiag::{thomas,bfb,cr}  (src/algorithm/ekat_tridiag.hpp)
   ekat_b200.lin_interp.LinInterp           <- ekat::LinInterp                (src/algorithm/ekat_lin_interp.hpp)
+  ekat_b200.reduction.view_reduction       <- ekat::ReductionUtils::view_reduction (src/algorithm/ekat_reduction_utils.hpp)
   ekat_b200.comm.Comm                      <- ekat::Comm                     (src/core/ekat_comm.hpp)
 
 PyTorch is used for device memory, streams and torch.distributed only. There is no CPU or

@@ -44,6 +44,9 @@ int col_to_lev(const R* src, R* dst, int64_t ncol, int n, int64_t src_stride, in
 template <typename R>
 int lev_to_col(const R* src, R* dst, int64_t ncol, int n, int64_t pitch, int64_t dst_stride, cudaStream_t st);
 template <typename R>
+int view_reduction(const R* in, R* out, int64_t ncol, int begin, int end, int64_t pitch, int col_major, int packn,
+                   cudaStream_t st);
+template <typename R>
 int checksum(const R* a, int64_t nrows, int64_t ncol, int64_t pitch, uint64_t* out, cudaStream_t st);
 template <typename R>
 int residual(const R* dl, const R* d, const R* du, const R* B, const R* X, int64_t ncol, int nlev, int nA, int nrhs,
@@ -209,6 +212,16 @@ DEF_LI_LM(float, f32)
     if (ncol < 0 || n < 0 || dst_stride < n || pitch < ncol) return EKAT_B200_ERR_INVALID;                     \
     if (ncol && n && (!src || !dst)) return EKAT_B200_ERR_INVALID;                                             \
     return lev_to_col<T>(src, dst, ncol, n, pitch, dst_stride, ST(s));                                         \
+  }                                                                                                            \
+  int ekat_b200_view_reduction_##sfx(const T* in, T* out, int64_t ncol, int begin, int end, int64_t pitch,     \
+                                     ekat_b200_layout layout, int pack_n, ekat_b200_stream_t s) {             \
+    if (ncol < 0 || begin < 0 || end < begin || pack_n < 0) return EKAT_B200_ERR_INVALID;                      \
+    if (layout != EKAT_B200_LAYOUT_COL_MAJOR && layout != EKAT_B200_LAYOUT_LEV_MAJOR) return EKAT_B200_ERR_INVALID; \
+    const int64_t need = pack_n > 1 ? ((int64_t)(end + pack_n - 1) / pack_n) * pack_n : end;                   \
+    if (layout == EKAT_B200_LAYOUT_COL_MAJOR ? pitch < need : pitch < ncol) return EKAT_B200_ERR_INVALID;      \
+    if (ncol && (!in || !out)) return EKAT_B200_ERR_INVALID;                                                   \
+    return view_reduction<T>(in, out, ncol, begin, end, pitch, layout == EKAT_B200_LAYOUT_COL_MAJOR, pack_n,   \
+                             ST(s));                                                                           \
   }                                                                                                            \
   int ekat_b200_checksum_##sfx(const T* a, int64_t nrows, int64_t ncol, int64_t pitch, uint64_t* out,          \
                                ekat_b200_stream_t s) {                                                         \

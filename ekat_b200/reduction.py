@@ -1,0 +1,43 @@
+"""Per-column vertical sums on torch CUDA tensors -- the Python face of
+ekat::ReductionUtils<ExeSpace,Serialize>::view_reduction (reference:
+src/algorithm/ekat_reduction_utils.hpp:67-144, 156-179; call form tests/algorithm/reduction_tests.cpp:117-126).
+
+Where the reference is called once per column inside the caller's team kernel, this takes the whole batch
+(SURVEY.md section 8b / 8f-2). The summation order is the reference's, so results are bit-identical to its host build:
+  serialize=True   (ekatBFB):  element after element over the scalar range [begin, end);
+  serialize=False, pack=N:     leading partial pack, per-lane sums of the full packs added in lane order, trailing
+                               partial pack (what a team computes for a view of Pack<Real,N>).
+Shapes: COL_MAJOR x [ncol, pitch] (the reference's rows of npack*N scalars; dim-0 may be strided);
+        LEV_MAJOR x [nlev, pitch] (columns fastest).
+"""
+import torch
+
+from . import COL_MAJOR, LEV_MAJOR
+from ._lib import lib, check
+
+_SFX = {torch.float64: "f64", torch.float32: "f32"}
+
+
+def view_reduction(x, begin=0, end=None, serialize=True, pack=1, layout=COL_MAJOR, ncol=None, out=None):
+    if not x.is_cuda or x.dtype not in _SFX or x.dim() != 2 or (x.numel() > 0 and x.shape[1] > 1 and x.stride(1) != 1):
+        raise ValueError("view_reduction needs a 2-D float32/float64 CUDA tensor with unit last stride (no CPU path)")
+    if layout == COL_MAJOR:
+        nc, width = x.shape
+        pitch = x.stride(0) if nc > 1 else width
+        end = width if end is None else end
+    elif layout == LEV_MAJOR:
+        nlev, width = x.shape
+        nc = width if ncol is None else ncol
+        pitch = x.stride(0) if nlev > 1 else width
+        end = nlev if end is None else end
+        need = -(-end // pack) * pack if (not serialize and pack > 1) else end
+        if need > nlev or nc > width:
+            raise ValueError("view_reduction: range exceeds the array")
+    else:
+        raise ValueError("unknown layout")
+    if out is None:
+        out = torch.empty(nc, dtype=x.dtype, device=x.device)
+    fn = f"ekat_b200_view_reduction_{_SFX[x.dtype]}"
+    check(fn, getattr(lib(), fn)(x.data_ptr(), out.data_ptr(), nc, int(begin), int(end), pitch, layout,
+                                 0 if serialize else int(pack), torch.cuda.current_stream().cuda_stream))
+    return out

@@ -177,6 +177,26 @@ int ekat_b200_lev_to_col_f32(const float* src, float* dst, int64_t ncol, int n, 
                              int64_t dst_stride, ekat_b200_stream_t stream);
 
 /* ------------------------------------------------------------------------
+ * ekat::ReductionUtils<ExeSpace,Serialize>::view_reduction for every column
+ * (reference src/algorithm/ekat_reduction_utils.hpp:
+ * 67-144, 156-179; call form tests/algorithm/reduction_tests.cpp:117-126):
+ * out[c] = sum of column c over the SCALAR range [begin, end).
+ *   layout COL_MAJOR: in[c*pitch + k] (the reference's [ncol][npack*N] rows);
+ *   layout LEV_MAJOR: in[k*pitch + c].
+ *   pack_n == 0: Serialize = true  -- element after element, in order;
+ *   pack_n >= 1: Serialize = false over Pack<Real,pack_n> -- leading partial
+ *                pack, per-lane sums of the full packs added in lane order,
+ *                trailing partial pack, exactly as the reference orders them.
+ * Either way the order is fixed: bit-identical to the reference's host build.
+ * Scalars outside what that order reads (pack padding) are never touched.
+ * COL_MAJOR needs pitch >= npack(end)*pack_n; LEV_MAJOR that many rows.
+ * ---------------------------------------------------------------------- */
+int ekat_b200_view_reduction_f64(const double* in, double* out, int64_t ncol, int begin, int end, int64_t pitch,
+                                 ekat_b200_layout layout, int pack_n, ekat_b200_stream_t stream);
+int ekat_b200_view_reduction_f32(const float* in, float* out, int64_t ncol, int begin, int end, int64_t pitch,
+                                 ekat_b200_layout layout, int pack_n, ekat_b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
  * Verification reductions for the column-sharded multi-GPU driver (SURVEY.md
  * section 8e). Results are DEVICE scalars so they can go straight into one
  * NCCL all-reduce (ekat::Comm::all_reduce, src/core/ekat_comm.hpp:152-162).

@@ -8,6 +8,7 @@
 #include <Kokkos_Core.hpp>  // the stand-in: only its View type is used
 
 #include "ekat_b200/ekat_lin_interp.hpp"
+#include "ekat_b200/ekat_reduction_utils.hpp"
 #include "ekat_b200/ekat_tridiag.hpp"
 
 template <class S> using VR2 = Kokkos::View<S**, Kokkos::LayoutRight, Kokkos::MemoryUnmanaged>;
@@ -81,6 +82,25 @@ int main(int argc, char** argv) {
     lp.setup(xp, xq);
     VR2<const double> wrong(fake, 0, 72);  // scalar view must be npack*N = 80 wide
     bad += !throws_invalid([&] { lp.setup(wrong, xq); });
+  }
+  // ReductionUtils::view_reduction: empty batches in both layouts / pack sizes; range and extent checks
+  {
+    using V1d = Kokkos::View<double*, Kokkos::LayoutRight, Kokkos::MemoryUnmanaged>;
+    using V1f = Kokkos::View<float*, Kokkos::LayoutRight, Kokkos::MemoryUnmanaged>;
+    VR2<const double> d0(fake, 0, 128);
+    V1d r0(fake, 0);
+    ekat::b200::ReductionUtils<>::view_reduction(nullptr, 0, 128, d0, r0);
+    ekat::b200::ReductionUtils<false>::view_reduction(nullptr, 3, 100, d0, r0);
+    VR2<const Pack16> p0(reinterpret_cast<const Pack16*>(fake), 0, 8);
+    ekat::b200::ReductionUtils<false>::view_reduction(nullptr, 0, 128, p0, r0);
+    VL2<float> l0(fakef, 0, 72);
+    V1f rf(fakef, 0);
+    ekat::b200::ReductionUtils<true>::view_reduction(nullptr, 0, 72, l0, rf);
+    VR2<const double> d8(fake, 8, 128);
+    V1d r8(fake, 8), r9(fake, 9);
+    bad += !throws_invalid([&] { ekat::b200::ReductionUtils<>::view_reduction(nullptr, 0, 129, d8, r8); });  // end beyond the view
+    bad += !throws_invalid([&] { ekat::b200::ReductionUtils<>::view_reduction(nullptr, 5, 4, d8, r8); });    // end < begin
+    bad += !throws_invalid([&] { ekat::b200::ReductionUtils<>::view_reduction(nullptr, 0, 128, d8, r9); });  // results extent
   }
   if (bad) {
     std::printf("adapter argument checks FAILED (%d)\n", bad);

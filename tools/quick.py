@@ -1,9 +1,8 @@
 import sys; sys.path.insert(0,"tools"); sys.path.insert(0,".")
 import sweep, ekat_b200
-V=[(0,0,0),(0,0,10),(0,0,11)]
-for nlev in (32,64,72,96,128,160,256):
-    sweep.tridiag_case("bfb","f64",345600*128//nlev,nlev, tunings=V)
-for nlev in (72,128,256):
-    sweep.tridiag_case("bfb","f32",345600*128//nlev,nlev, tunings=V)
-    sweep.tridiag_case("bfb","f64",345600*128//nlev,nlev, layout=ekat_b200.COL_MAJOR, tunings=V)
-    sweep.tridiag_case("bfb","f32",345600*128//nlev,nlev, layout=ekat_b200.COL_MAJOR, tunings=V)
+for dt in ("f64","f32"):
+    for lay in (ekat_b200.COL_MAJOR, ekat_b200.LEV_MAJOR):
+        for ser in (True, False):
+            sweep.reduction_case(dt, 3145728, 128, layout=lay, serialize=ser)
+sweep.reduction_case("f64", 345600, 128)
+sweep.reduction_case("f64", 345600, 72)

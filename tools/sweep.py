@@ -113,6 +113,20 @@ def fused_case(dt, ncol, nlev, km2, nrhs, tunings=((0, 0, 0),)):
                col_lev_per_s=ncol * nlev / ms * 1e3, gbs=round(alg / ms / 1e6, 1), frac=round(alg / ms / 1e6 / PEAK, 3))
 
 
+def reduction_case(dt, ncol, nlev, layout=ekat_b200.COL_MAJOR, serialize=True, pack=16):
+    from ekat_b200.reduction import view_reduction
+    tdt = torch.float64 if dt == "f64" else torch.float32
+    w = 8 if dt == "f64" else 4
+    x = torch.rand((ncol, nlev) if layout == ekat_b200.COL_MAJOR else (nlev, ncol), dtype=tdt, device=dev)
+    out = torch.empty(ncol, dtype=tdt, device=dev)
+    alg = nlev * w * ncol
+    small = alg < (200 << 20)
+    ms = timeit(lambda: view_reduction(x, 0, nlev, serialize=serialize, pack=pack, layout=layout, out=out), flush=small)
+    report(kernel="view_reduction", variant=lib().ekat_b200_last_kernel().decode(), dt=dt, ncol=ncol, nlev=nlev,
+           layout="lev" if layout else "col", serialize=serialize, pack=pack, ms=round(ms, 4), col_lev_per_s=ncol * nlev / ms * 1e3,
+           gbs=round(alg / ms / 1e6, 1), frac=round(alg / ms / 1e6 / PEAK, 3), l2_flushed=small)
+
+
 def copy_peak():
     n = 1 << 30
     a = torch.empty(n, dtype=torch.uint8, device=dev)
