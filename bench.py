@@ -319,6 +319,10 @@ def run_extras(torch, dev, peak):
             if restore:
                 restore()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            # keep the device busy for ~0.1 ms while the host enqueues: the interval between the two events is then the
+            # kernel's own duration, not the host's launch path (tensor-map encoding + ctypes: ~30 us, which is more
+            # than the whole kernel at config 1 size)
+            torch.cuda._sleep(200_000)
             a.record()
             fn()
             b.record()
@@ -347,7 +351,8 @@ def run_extras(torch, dev, peak):
     tri("config 3, cr (bit-exact), level-major", "cr", 345600, 128, 1, 1, LM)
     tri("config 3, thomas, level-major", "thomas", 345600, 128, 1, 1, LM)
     tri("config 3, bfb (bit-exact), level-major", "bfb", 345600, 128, 1, 1, LM)
-    tri("config 1, thomas, 21,600 x 72 (fits L2; launch-latency bound)", "thomas", 21600, 72, 1, 1, LM)
+    tri("config 1, thomas, 21,600 x 72 (62 MB: L2-resident after the warm-up launches)", "thomas", 21600, 72, 1, 1, LM)
+    tri("config 1, bfb (bit-exact), 21,600 x 72 (L2-resident)", "bfb", 21600, 72, 1, 1, LM)
     for km1, N, label in ((72, 16, "config 2, LinInterp 72->128, Pack<double,16> pitch"), (72, 1, "config 2, LinInterp 72->128, scalar pitch")):
         ncol = 345600
         x1, y1, x2 = li_fill(torch.float64, ncol, km1, 128, N, device=dev)
@@ -368,6 +373,23 @@ def run_extras(torch, dev, peak):
     out.append({"case": "config 4, 10-rhs thomas + LinInterp 128->128 of the 10 solutions (25,600 B/column algorithmic)",
                 "kernel": "tridiag_tma_shared<f64,thomas> + " + lib().ekat_b200_last_kernel().decode(), "ms": ms,
                 "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak, "col_lev_per_s": ncol * 128 / ms * 1e3})
+    del dl, d, du, Bm, x1, x2, Y2
+    torch.cuda.empty_cache()
+    # ReductionUtils::view_reduction and the layout marshalling, config 5 shard size
+    from ekat_b200.reduction import view_reduction
+    ncol = 3145728
+    x = torch.rand((ncol, 128), dtype=torch.float64, device=dev)
+    res = torch.empty(ncol, dtype=torch.float64, device=dev)
+    for ser, label in ((True, "Serialize (bit-for-bit order)"), (False, "Pack<double,16> order")):
+        ms = timed(lambda: view_reduction(x, 0, 128, serialize=ser, pack=16, out=res))
+        alg = 128 * 8 * ncol
+        out.append({"case": f"8f-2 view_reduction, {ncol} x 128 f64, reference layout, {label}",
+                    "kernel": lib().ekat_b200_last_kernel().decode(), "ms": ms, "gbs": alg / ms / 1e6,
+                    "frac": alg / ms / 1e6 / peak, "col_lev_per_s": ncol * 128 / ms * 1e3})
+    ms = timed(lambda: T.col_to_lev(x))
+    alg = 2 * 128 * 8 * ncol
+    out.append({"case": f"8f-1 marshalling [col][lev] -> [lev][col], {ncol} x 128 f64 (read + write)", "kernel": lib().ekat_b200_last_kernel().decode(),
+                "ms": ms, "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak, "col_lev_per_s": ncol * 128 / ms * 1e3})
     return out
 
 
