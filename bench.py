@@ -386,6 +386,13 @@ def run_extras(torch, dev, peak):
         out.append({"case": f"8f-2 view_reduction, {ncol} x 128 f64, reference layout, {label}",
                     "kernel": lib().ekat_b200_last_kernel().decode(), "ms": ms, "gbs": alg / ms / 1e6,
                     "frac": alg / ms / 1e6 / peak, "col_lev_per_s": ncol * 128 / ms * 1e3})
+    from ekat_b200.reduction import adj_diff
+    dxo = torch.empty_like(x)
+    ms = timed(lambda: adj_diff(x, True, out=dxo))
+    alg = 2 * 128 * 8 * ncol
+    out.append({"case": f"8f-3 adj_diff<Forward>, {ncol} x 128 f64, reference layout (read + write)", "kernel": lib().ekat_b200_last_kernel().decode(),
+                "ms": ms, "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak, "col_lev_per_s": ncol * 128 / ms * 1e3})
+    del dxo
     ms = timed(lambda: T.col_to_lev(x))
     alg = 2 * 128 * 8 * ncol
     out.append({"case": f"8f-1 marshalling [col][lev] -> [lev][col], {ncol} x 128 f64 (read + write)", "kernel": lib().ekat_b200_last_kernel().decode(),

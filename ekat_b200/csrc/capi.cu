@@ -44,6 +44,9 @@ int col_to_lev(const R* src, R* dst, int64_t ncol, int n, int64_t src_stride, in
 template <typename R>
 int lev_to_col(const R* src, R* dst, int64_t ncol, int n, int64_t pitch, int64_t dst_stride, cudaStream_t st);
 template <typename R>
+int adj_diff(const R* in, R* out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out, int col_major, int forward,
+             cudaStream_t st);
+template <typename R>
 int view_reduction(const R* in, R* out, int64_t ncol, int begin, int end, int64_t pitch, int col_major, int packn,
                    cudaStream_t st);
 template <typename R>
@@ -212,6 +215,16 @@ DEF_LI_LM(float, f32)
     if (ncol < 0 || n < 0 || dst_stride < n || pitch < ncol) return EKAT_B200_ERR_INVALID;                     \
     if (ncol && n && (!src || !dst)) return EKAT_B200_ERR_INVALID;                                             \
     return lev_to_col<T>(src, dst, ncol, n, pitch, dst_stride, ST(s));                                         \
+  }                                                                                                            \
+  int ekat_b200_adj_diff_##sfx(const T* in, T* out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out,  \
+                               ekat_b200_layout layout, int forward, ekat_b200_stream_t s) {                  \
+    if (ncol < 0 || n < 0) return EKAT_B200_ERR_INVALID;                                                       \
+    if (layout != EKAT_B200_LAYOUT_COL_MAJOR && layout != EKAT_B200_LAYOUT_LEV_MAJOR) return EKAT_B200_ERR_INVALID; \
+    const int64_t need = layout == EKAT_B200_LAYOUT_COL_MAJOR ? (int64_t)n : ncol;                             \
+    if (pitch_in < need || pitch_out < need) return EKAT_B200_ERR_INVALID;                                     \
+    if (ncol && n && (!in || !out || in == out)) return EKAT_B200_ERR_INVALID;                                 \
+    return adj_diff<T>(in, out, ncol, n, pitch_in, pitch_out, layout == EKAT_B200_LAYOUT_COL_MAJOR, forward,   \
+                       ST(s));                                                                                 \
   }                                                                                                            \
   int ekat_b200_view_reduction_##sfx(const T* in, T* out, int64_t ncol, int begin, int end, int64_t pitch,     \
                                      ekat_b200_layout layout, int pack_n, ekat_b200_stream_t s) {             \

@@ -1,0 +1,128 @@
+// column_ops.cu -- ekat::adj_diff for every index of every column of a batch.
+//
+// Replaces the per-column, per-index loop around ekat::adj_diff<Forward>(view, index, index_end) (reference
+// src/pack/ekat_pack_kokkos.hpp:100-164; call form tests/pack/pack_kokkos_utils.cpp:1055-1080) -- the finite-difference
+// step column physics runs right before it fills (dl, d, du):
+//   Forward : out[k] = (k < n-1 ? in[k+1] : 0) - in[k]          (:149-152; packs: :118-121)
+//   backward: out[k] = in[k] - (k > 0 ? in[k-1] : 0)            (:153-157; packs: :122-126)
+// over the n scalars of the (scalarized) column; for a view of Pack<Real,N> n = npack*N, padding lanes included, exactly
+// as the reference's shift_left / shift_right with a 0 fill behave. One rounded subtraction per element: bit-identical.
+//
+// Roofline: HBM, 2 * n * word bytes per column (one read, one write).
+//   COL_MAJOR in[c*pitch + k]: 16-byte vectors along the column, the neighbour element across the vector boundary is a
+//     second (L1-resident) scalar load;
+//   LEV_MAJOR in[k*pitch + c]: one thread per column walks the levels with the previous row in a register and eight
+//     rows in flight, so every row is read from HBM once.
+#include "tridiag_lm_common.cuh"  // Vec
+
+namespace ekb {
+
+// One work item = one 16-byte vector (VEC scalars) of one column, or one scalar when the operands are not 16-byte
+// aligned; items are dealt out flat over the whole batch so that no thread idles whatever the column length is.
+template <typename R, bool FWD, bool VECTOR>
+__global__ void __launch_bounds__(256)
+k_adj_diff_cm(const R* __restrict__ in, R* __restrict__ out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out) {
+  constexpr int VEC = VECTOR ? 16 / sizeof(R) : 1;
+  const unsigned per_col = (unsigned)(n / VEC);  // n % VEC == 0 when VECTOR
+  const int64_t items = ncol * per_col;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < items; i += (int64_t)gridDim.x * 256) {
+    const int64_t c = items < ((int64_t)1 << 32) ? (int64_t)((unsigned)i / per_col) : i / per_col;
+    const int k0 = (int)(i - c * per_col) * VEC;
+    const R* x = in + (size_t)c * pitch_in;
+    R* o = out + (size_t)c * pitch_out;
+    if (VECTOR) {
+      Vec<R, VEC> v = *reinterpret_cast<const Vec<R, VEC>*>(x + k0), r;
+      if (FWD) {
+        const R nxt = k0 + VEC < n ? __ldg(x + k0 + VEC) : (R)0;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) r.v[j] = x_sub(j + 1 < VEC ? v.v[j + 1] : nxt, v.v[j]);
+      } else {
+        const R prv = k0 > 0 ? __ldg(x + k0 - 1) : (R)0;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) r.v[j] = x_sub(v.v[j], j > 0 ? v.v[j - 1] : prv);
+      }
+      *reinterpret_cast<Vec<R, VEC>*>(o + k0) = r;
+    } else {
+      if (FWD) o[k0] = x_sub(k0 < n - 1 ? __ldg(x + k0 + 1) : (R)0, __ldg(x + k0));
+      else o[k0] = x_sub(__ldg(x + k0), k0 > 0 ? __ldg(x + k0 - 1) : (R)0);
+    }
+  }
+}
+
+template <typename R, bool FWD>
+__global__ void __launch_bounds__(128)
+k_adj_diff_lm(const R* __restrict__ in, R* __restrict__ out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out) {
+  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ncol) return;
+  const R* x = in + c;
+  R* o = out + c;
+  if (FWD) {
+    R cur = n > 0 ? ld_stream(x) : (R)0;
+    int k = 0;
+    for (; k + 8 < n; k += 8) {  // rows k+1 .. k+8 exist
+      R v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = ld_stream(x + (size_t)(k + 1 + u) * pitch_in);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        st_stream(o + (size_t)(k + u) * pitch_out, x_sub(v[u], cur));
+        cur = v[u];
+      }
+    }
+    for (; k < n; ++k) {
+      const R nxt = k < n - 1 ? ld_stream(x + (size_t)(k + 1) * pitch_in) : (R)0;
+      st_stream(o + (size_t)k * pitch_out, x_sub(nxt, cur));
+      cur = nxt;
+    }
+  } else {
+    R prv = (R)0;
+    int k = 0;
+    for (; k + 8 <= n; k += 8) {
+      R v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = ld_stream(x + (size_t)(k + u) * pitch_in);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        st_stream(o + (size_t)(k + u) * pitch_out, x_sub(v[u], prv));
+        prv = v[u];
+      }
+    }
+    for (; k < n; ++k) {
+      const R v = ld_stream(x + (size_t)k * pitch_in);
+      st_stream(o + (size_t)k * pitch_out, x_sub(v, prv));
+      prv = v;
+    }
+  }
+}
+
+template <typename R>
+int adj_diff(const R* in, R* out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out, int col_major, int forward,
+             cudaStream_t st) {
+  if (ncol == 0 || n == 0) return EKAT_B200_OK;
+  if (!col_major) {
+    const unsigned blocks = (unsigned)((ncol + 127) / 128);
+    if (forward) k_adj_diff_lm<R, true><<<blocks, 128, 0, st>>>(in, out, ncol, n, pitch_in, pitch_out);
+    else k_adj_diff_lm<R, false><<<blocks, 128, 0, st>>>(in, out, ncol, n, pitch_in, pitch_out);
+    note_launch(sizeof(R) == 8 ? "adj_diff_lm<f64>" : "adj_diff_lm<f32>");
+    return check_cuda(cudaGetLastError());
+  }
+  constexpr int VEC = 16 / sizeof(R);
+  const int vec_ok = n % VEC == 0 && pitch_in % VEC == 0 && pitch_out % VEC == 0 &&
+                     (reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+  const int64_t items = ncol * (vec_ok ? n / VEC : n);
+  const unsigned blocks = (unsigned)tmin<int64_t>((items + 255) / 256, (int64_t)148 * 8 * 64);
+  if (vec_ok) {
+    if (forward) k_adj_diff_cm<R, true, true><<<blocks, 256, 0, st>>>(in, out, ncol, n, pitch_in, pitch_out);
+    else k_adj_diff_cm<R, false, true><<<blocks, 256, 0, st>>>(in, out, ncol, n, pitch_in, pitch_out);
+  } else {
+    if (forward) k_adj_diff_cm<R, true, false><<<blocks, 256, 0, st>>>(in, out, ncol, n, pitch_in, pitch_out);
+    else k_adj_diff_cm<R, false, false><<<blocks, 256, 0, st>>>(in, out, ncol, n, pitch_in, pitch_out);
+  }
+  note_launch(sizeof(R) == 8 ? "adj_diff_cm<f64>" : "adj_diff_cm<f32>");
+  return check_cuda(cudaGetLastError());
+}
+
+template int adj_diff<double>(const double*, double*, int64_t, int, int64_t, int64_t, int, int, cudaStream_t);
+template int adj_diff<float>(const float*, float*, int64_t, int, int64_t, int64_t, int, int, cudaStream_t);
+
+}  // namespace ekb

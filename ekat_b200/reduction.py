@@ -41,3 +41,27 @@ def view_reduction(x, begin=0, end=None, serialize=True, pack=1, layout=COL_MAJO
     check(fn, getattr(lib(), fn)(x.data_ptr(), out.data_ptr(), nc, int(begin), int(end), pitch, layout,
                                  0 if serialize else int(pack), torch.cuda.current_stream().cuda_stream))
     return out
+
+
+def adj_diff(x, forward=True, layout=COL_MAJOR, ncol=None, out=None):
+    """ekat::adj_diff<Forward> at every index of every column (reference src/pack/ekat_pack_kokkos.hpp:100-164):
+    forward: out[k] = (k < n-1 ? x[k+1] : 0) - x[k]; backward: out[k] = x[k] - (k > 0 ? x[k-1] : 0), over the n scalars
+    of the scalarized column (a Pack view's padding lanes take part, as in the reference).
+    COL_MAJOR x [ncol, n] (dim-0 may be strided); LEV_MAJOR x [n, pitch]."""
+    if not x.is_cuda or x.dtype not in _SFX or x.dim() != 2 or (x.numel() > 0 and x.shape[1] > 1 and x.stride(1) != 1):
+        raise ValueError("adj_diff needs a 2-D float32/float64 CUDA tensor with unit last stride (no CPU path)")
+    if out is None:
+        out = torch.empty(x.shape, dtype=x.dtype, device=x.device)
+    if out.shape != x.shape or out.dtype != x.dtype or (out.numel() > 0 and out.shape[1] > 1 and out.stride(1) != 1):
+        raise ValueError("adj_diff: out must match x")
+    if layout == COL_MAJOR:
+        nc, n = x.shape
+        pin, pout = (x.stride(0) if nc > 1 else n), (out.stride(0) if nc > 1 else n)
+    else:
+        n, width = x.shape
+        nc = width if ncol is None else ncol
+        pin, pout = (x.stride(0) if n > 1 else width), (out.stride(0) if n > 1 else width)
+    fn = f"ekat_b200_adj_diff_{_SFX[x.dtype]}"
+    check(fn, getattr(lib(), fn)(x.data_ptr(), out.data_ptr(), nc, n, pin, pout, layout, 1 if forward else 0,
+                                 torch.cuda.current_stream().cuda_stream))
+    return out

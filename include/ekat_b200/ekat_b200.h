@@ -197,6 +197,23 @@ int ekat_b200_view_reduction_f32(const float* in, float* out, int64_t ncol, int 
                                  ekat_b200_layout layout, int pack_n, ekat_b200_stream_t stream);
 
 /* ------------------------------------------------------------------------
+ * ekat::adj_diff<Forward> at every index of every column (SURVEY.md section
+ * 8f-3; reference src/pack/ekat_pack_kokkos.hpp:100-164; call form
+ * tests/pack/pack_kokkos_utils.cpp:1055-1080) -- the finite-difference step
+ * in front of a tridiagonal fill:
+ *   forward != 0: out[k] = (k < n-1 ? in[k+1] : 0) - in[k]
+ *   forward == 0: out[k] = in[k] - (k > 0 ? in[k-1] : 0)
+ * over the n scalars of the scalarized column (for Pack<Real,N> views n =
+ * npack*N: padding lanes take part, as in the reference). in != out.
+ *   layout COL_MAJOR: in[c*pitch_in + k], out[c*pitch_out + k];
+ *   layout LEV_MAJOR: in[k*pitch_in + c], out[k*pitch_out + c].
+ * ---------------------------------------------------------------------- */
+int ekat_b200_adj_diff_f64(const double* in, double* out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out,
+                           ekat_b200_layout layout, int forward, ekat_b200_stream_t stream);
+int ekat_b200_adj_diff_f32(const float* in, float* out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out,
+                           ekat_b200_layout layout, int forward, ekat_b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
  * Verification reductions for the column-sharded multi-GPU driver (SURVEY.md
  * section 8e). Results are DEVICE scalars so they can go straight into one
  * NCCL all-reduce (ekat::Comm::all_reduce, src/core/ekat_comm.hpp:152-162).

@@ -1,4 +1,4 @@
-// ekat_reduction_utils.hpp (ekat_b200) -- host adapter that keeps the ekat::ReductionUtils entry point
+// ekat_reduction_utils.hpp (ekat_b200) -- host adapters that keep the ekat::ReductionUtils entry point and ekat::adj_diff
 // (reference: src/algorithm/ekat_reduction_utils.hpp:156-179) on top of the C ABI in ekat_b200.h.
 //
 // The reference's view_reduction is a team-level device function called once per column inside the caller's
@@ -58,6 +58,47 @@ struct ReductionUtils {
     if (rc != EKAT_B200_OK) throw std::runtime_error(std::string("ekat_b200_view_reduction: ") + ekat_b200_last_cuda_error());
   }
 };
+
+// ekat::adj_diff<Forward>(view, index, index_end) at every index of every column (reference
+// src/pack/ekat_pack_kokkos.hpp:100-164; tests/pack/pack_kokkos_utils.cpp:1055-1080 loops it over a view):
+//     ekat::b200::adj_diff<Forward>(stream, in, out);       in, out: (ncol, nlev) views of Real or Pack<Real,N>
+// A Pack view is differenced over its npack*N scalars, padding lanes included, as the reference's shift_left /
+// shift_right with a 0 fill do. in and out must not alias.
+template <bool Forward, typename InView, typename OutView>
+void adj_diff(ekat_b200_stream_t stream, const InView& in, const OutView& out) {
+  using value_type = typename std::remove_const<typename InView::value_type>::type;
+  using out_type = typename std::remove_const<typename OutView::value_type>::type;
+  using scalar = typename std::remove_const<typename tridiag::b200_impl::pack_scalar<value_type>::type>::type;
+  static_assert(InView::rank == 2 && OutView::rank == 2, "adj_diff: (ncol, nlev) views");
+  static_assert(std::is_same<value_type, out_type>::value, "adj_diff: in and out share a value type");
+  static_assert(std::is_same<scalar, double>::value || std::is_same<scalar, float>::value, "double or float");
+  static_assert(std::is_same<typename InView::array_layout, typename OutView::array_layout>::value, "adj_diff: one layout");
+  constexpr int pack = sizeof(value_type) / sizeof(scalar);
+  constexpr int layout = tridiag::b200_impl::layout_code<typename InView::array_layout>::value;
+  const long long ncol = in.extent_int(0);
+  const int n = in.extent_int(1) * pack;
+  if (out.extent_int(0) != ncol || out.extent_int(1) != in.extent_int(1)) throw std::invalid_argument("adj_diff: extents differ");
+  if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && pack != 1) throw std::invalid_argument("adj_diff: packed level-major views are not supported");
+  if (ncol == 0 || n == 0) return;
+  if (static_cast<const void*>(in.data()) == static_cast<const void*>(out.data())) throw std::invalid_argument("adj_diff: in and out alias");
+  long long pin, pout;
+  if (layout == EKAT_B200_LAYOUT_COL_MAJOR) {
+    pin = ncol > 1 ? (long long)in.stride(0) * pack : n;
+    pout = ncol > 1 ? (long long)out.stride(0) * pack : n;
+  } else {
+    pin = in.stride(1);
+    pout = out.stride(1);
+  }
+  const scalar* pi = reinterpret_cast<const scalar*>(in.data());
+  scalar* po = const_cast<scalar*>(reinterpret_cast<const scalar*>(out.data()));
+  int rc;
+  if constexpr (std::is_same<scalar, double>::value)
+    rc = ekat_b200_adj_diff_f64(pi, po, ncol, n, pin, pout, (ekat_b200_layout)layout, Forward ? 1 : 0, stream);
+  else
+    rc = ekat_b200_adj_diff_f32(pi, po, ncol, n, pin, pout, (ekat_b200_layout)layout, Forward ? 1 : 0, stream);
+  if (rc == EKAT_B200_ERR_INVALID) throw std::invalid_argument("ekat_b200_adj_diff: invalid argument");
+  if (rc != EKAT_B200_OK) throw std::runtime_error(std::string("ekat_b200_adj_diff: ") + ekat_b200_last_cuda_error());
+}
 
 }  // namespace b200
 }  // namespace ekat

@@ -163,6 +163,23 @@ class CpuOracle:
         return out
 
 
+    def adj_diff(self, x, forward=True, packn=0):
+        """ekat::adj_diff at every index of every column of x [ncol, pitch] (packn: 0 = scalar view, N = Pack<Real,N>)."""
+        x = np.ascontiguousarray(x)
+        ncol, pitch = x.shape
+        out = np.zeros_like(x)
+        s = _sfx(x.dtype)
+        if self.kind == "port":
+            rc = getattr(self.lib, "ekat_oracle_adj_diff_" + s)(_p(x), _p(out), _i64(ncol), _int(pitch), _i64(pitch),
+                                                                _int(1 if forward else 0))
+        else:
+            rc = getattr(self.lib, "ekat_ref_adj_diff_" + s)(_int(packn), _int(1 if forward else 0), _p(x), _p(out),
+                                                             _i64(ncol), _i64(pitch))
+        if rc != 0:
+            raise ValueError(f"{self.kind} oracle adj_diff rc={rc}")
+        return out
+
+
 _cache = {}
 
 

@@ -47,6 +47,18 @@ def main():
                 out[key + "_ser"] = r.view_reduction(x, b, e, 0)
                 out[key + "_pack"] = r.view_reduction(x, b, e, N)
                 n += 1
+    # ekat::adj_diff (src/pack/ekat_pack_kokkos.hpp:100-164): the reference test's data i^2
+    # (tests/pack/pack_kokkos_utils.cpp:1040-1052) and seeded columns, scalar views and Pack 4 / 16 views
+    for dt in ("f64", "f32"):
+        dtype = np.float64 if dt == "f64" else np.float32
+        for pitch, N in [(16, 0), (16, 4), (128, 16), (80, 16), (72, 0), (7, 1), (1, 0)]:
+            rng = np.random.default_rng(77 + pitch + N)
+            x = (rng.standard_normal((24, pitch)) * 50).astype(dtype)
+            x[0] = (np.arange(pitch, dtype=np.float64) ** 2).astype(dtype)
+            key = f"adj_{dt}_{pitch}_{N}"
+            out[key + "_x"] = x
+            out[key + "_fwd"] = r.adj_diff(x, True, N)
+            out[key + "_bwd"] = r.adj_diff(x, False, N)
     np.savez_compressed(OUT, **out)
     print(OUT, n, "cases")
 

@@ -7,6 +7,7 @@
 // No reference source is copied here: this file only *calls*
 //   ekat::tridiag::{thomas,cr,bfb}       (src/algorithm/ekat_tridiag.hpp:323-678)
 //   ekat::LinInterp::{setup,lin_interp}  (src/algorithm/ekat_lin_interp.hpp:69-126)
+//   ekat::adj_diff<Forward>              (src/pack/ekat_pack_kokkos.hpp:100-164)
 //   ekat::impl::view_reduction<Serialize> (src/algorithm/ekat_reduction_utils.hpp:67-144)
 //   ekat::test::fill_tridiag_matrix / fill_data_matrix / matvec
 //                                        (tests/algorithm/tridiag_tests.hpp:11-88)
@@ -219,6 +220,42 @@ int view_reduction_n(const S* in, S* out, int64_t ncol, int begin, int end, int6
   });
   return 0;
 }
+// ekat::adj_diff<Forward> at every index of every column (src/pack/ekat_pack_kokkos.hpp:100-164), called as the
+// reference's test calls it on a view (tests/pack/pack_kokkos_utils.cpp:1061-1077): in, out [ncol][pitch] scalars.
+template <class S, int N, bool Forward>
+int adj_diff_n(const S* in, S* out, int64_t ncol, int64_t pitch) {
+  using P = ekat::Pack<S, N>;
+  if (pitch % N) return -3;
+  const int np = (int)(pitch / N);
+  Kokkos::parallel_for(Policy((int)ncol, 1), [&](const Member& team) {
+    const int c = team.league_rank();
+    V1<const P> row(reinterpret_cast<const P*>(in + (size_t)c * pitch), np);
+    P* o = reinterpret_cast<P*>(out + (size_t)c * pitch);
+    for (int i = 0; i < np; ++i) o[i] = ekat::adj_diff<Forward>(row, i, np);
+  });
+  return 0;
+}
+template <class S, bool Forward>
+int adj_diff_s(const S* in, S* out, int64_t ncol, int64_t pitch) {  // scalar views take the non-pack overload (:139-157)
+  Kokkos::parallel_for(Policy((int)ncol, 1), [&](const Member& team) {
+    const int c = team.league_rank();
+    V1<const S> row(in + (size_t)c * pitch, pitch);
+    for (int i = 0; i < (int)pitch; ++i) out[(size_t)c * pitch + i] = ekat::adj_diff<Forward>(row, i, (int)pitch);
+  });
+  return 0;
+}
+template <class S>
+int adj_diff(int packn, int forward, const S* in, S* out, int64_t ncol, int64_t pitch) {
+#define EKAT_REF_AD(N_) \
+  case N_: return forward ? adj_diff_n<S, N_, true>(in, out, ncol, pitch) : adj_diff_n<S, N_, false>(in, out, ncol, pitch);
+  switch (packn) {
+    case 0: return forward ? adj_diff_s<S, true>(in, out, ncol, pitch) : adj_diff_s<S, false>(in, out, ncol, pitch);
+    EKAT_REF_AD(1) EKAT_REF_AD(2) EKAT_REF_AD(4) EKAT_REF_AD(8) EKAT_REF_AD(16)
+    default: return -4;
+  }
+#undef EKAT_REF_AD
+}
+
 template <class S>
 int view_reduction(int packn, int serialize, const S* in, S* out, int64_t ncol, int begin, int end, int64_t pitch) {
 #define EKAT_REF_VR(N_) \
@@ -234,6 +271,12 @@ int view_reduction(int packn, int serialize, const S* in, S* out, int64_t ncol, 
 }  // namespace
 
 extern "C" {
+int ekat_ref_adj_diff_f64(int packn, int forward, const double* in, double* out, int64_t ncol, int64_t pitch) {
+  return adj_diff<double>(packn, forward, in, out, ncol, pitch);
+}
+int ekat_ref_adj_diff_f32(int packn, int forward, const float* in, float* out, int64_t ncol, int64_t pitch) {
+  return adj_diff<float>(packn, forward, in, out, ncol, pitch);
+}
 int ekat_ref_view_reduction_f64(int packn, int serialize, const double* in, double* out, int64_t ncol, int begin, int end,
                                 int64_t pitch) {
   return view_reduction<double>(packn, serialize, in, out, ncol, begin, end, pitch);

@@ -101,6 +101,15 @@ int main(int argc, char** argv) {
     bad += !throws_invalid([&] { ekat::b200::ReductionUtils<>::view_reduction(nullptr, 0, 129, d8, r8); });  // end beyond the view
     bad += !throws_invalid([&] { ekat::b200::ReductionUtils<>::view_reduction(nullptr, 5, 4, d8, r8); });    // end < begin
     bad += !throws_invalid([&] { ekat::b200::ReductionUtils<>::view_reduction(nullptr, 0, 128, d8, r9); });  // results extent
+    // adj_diff: empty batches, extents, aliasing
+    VR2<double> o0(fake, 0, 128), o8(fake + 4096, 8, 128), o7(fake + 4096, 8, 127), alias(fake, 8, 128);
+    ekat::b200::adj_diff<true>(nullptr, d0, o0);
+    ekat::b200::adj_diff<false>(nullptr, l0, VL2<float>(fakef, 0, 72));
+    VR2<Pack16> q0(reinterpret_cast<Pack16*>(fake), 0, 8);
+    ekat::b200::adj_diff<true>(nullptr, p0, q0);
+    bad += !throws_invalid([&] { ekat::b200::adj_diff<true>(nullptr, d8, o7); });     // extents differ
+    bad += !throws_invalid([&] { ekat::b200::adj_diff<true>(nullptr, d8, alias); });  // in == out
+    (void)o8;
   }
   if (bad) {
     std::printf("adapter argument checks FAILED (%d)\n", bad);

@@ -15,7 +15,7 @@ DT = {"f64": np.float64, "f32": np.float32}
 
 def gold_cases():
     g = np.load(GOLD)
-    for key in sorted(k[:-2] for k in g.files if k.endswith("_x")):
+    for key in sorted(k[:-2] for k in g.files if k.endswith("_x") and not k.startswith("adj_")):
         dt, tot, N, b, e = key.split("_")
         yield key, dt, int(tot), int(N), int(b), int(e), g[key + "_x"], g[key + "_ser"], g[key + "_pack"]
 
@@ -124,3 +124,50 @@ def test_gpu_view_reduction_full_size_property(cuda):
         rl = view_reduction(x.t().contiguous(), 0, nlev, serialize=ser, pack=16, layout=ekat_b200.LEV_MAJOR)
         assert torch.equal(rl, r)
         assert torch.allclose(r, x.sum(1), rtol=1e-13, atol=0)
+
+
+# ------------------------------------------------------------------------------------------------ adj_diff (8f-3)
+def adj_cases():
+    g = np.load(GOLD)
+    for key in sorted(k[:-2] for k in g.files if k.startswith("adj_") and k.endswith("_x")):
+        yield key, g[key + "_x"], g[key + "_fwd"], g[key + "_bwd"]
+
+
+def test_port_matches_golden_adj_diff(port):
+    n = 0
+    for key, x, fwd, bwd in adj_cases():
+        assert bits_equal(port.adj_diff(x, True), fwd) and bits_equal(port.adj_diff(x, False), bwd), key
+        n += 1
+    assert n == 14
+    # the reference's own check (tests/pack/pack_kokkos_utils.cpp:1051-1095): (i+1)^2 - i^2 = 2i+1, i^2 - (i-1)^2 = 2i-1
+    x = (np.arange(16, dtype=np.float64) ** 2)[None]
+    f, b = port.adj_diff(x, True)[0], port.adj_diff(x, False)[0]
+    assert np.array_equal(f[:-1], 2 * np.arange(15) + 1.0) and f[-1] == -225.0
+    assert np.array_equal(b[1:], 2 * np.arange(1, 16) - 1.0) and b[0] == 0.0
+
+
+@pytest.mark.gpu
+def test_gpu_adj_diff_matches_golden_and_oracle(cuda, port):
+    import torch
+    import ekat_b200
+    from ekat_b200.reduction import adj_diff
+    for key, x, fwd, bwd in adj_cases():
+        xd = torch.from_numpy(x).to(cuda)
+        assert bits_equal(adj_diff(xd, True).cpu().numpy(), fwd), key
+        assert bits_equal(adj_diff(xd, False).cpu().numpy(), bwd), key
+        xl = xd.t().contiguous()  # [n, ncol]
+        assert bits_equal(adj_diff(xl, True, layout=ekat_b200.LEV_MAJOR).t().contiguous().cpu().numpy(), fwd), key
+        assert bits_equal(adj_diff(xl, False, layout=ekat_b200.LEV_MAJOR).t().contiguous().cpu().numpy(), bwd), key
+    rng = np.random.default_rng(5)
+    for dt in (np.float64, np.float32):
+        for ncol, n in [(1, 1), (33, 129), (1000, 128), (4097, 72), (5, 3000), (0, 128)]:
+            x = (rng.standard_normal((ncol, n)) * 10).astype(dt)
+            wide = torch.zeros((ncol, n + 3), dtype=torch.from_numpy(x).dtype, device=cuda)  # odd pitch: the scalar path
+            wide[:, :n] = torch.from_numpy(x).to(cuda)
+            for f in (True, False):
+                want = port.adj_diff(x, f)
+                assert bits_equal(adj_diff(torch.from_numpy(x).to(cuda), f).cpu().numpy(), want), (ncol, n, f)
+                assert bits_equal(adj_diff(wide[:, :n], f).cpu().numpy(), want), (ncol, n, f, "strided")
+                if ncol:
+                    got = adj_diff(torch.from_numpy(np.ascontiguousarray(x.T)).to(cuda), f, layout=ekat_b200.LEV_MAJOR)
+                    assert bits_equal(got.cpu().numpy(), np.ascontiguousarray(want.T)), (ncol, n, f, "lev")

@@ -127,6 +127,19 @@ def reduction_case(dt, ncol, nlev, layout=ekat_b200.COL_MAJOR, serialize=True, p
            gbs=round(alg / ms / 1e6, 1), frac=round(alg / ms / 1e6 / PEAK, 3), l2_flushed=small)
 
 
+def adj_diff_case(dt, ncol, nlev, layout=ekat_b200.COL_MAJOR, forward=True):
+    from ekat_b200.reduction import adj_diff
+    tdt = torch.float64 if dt == "f64" else torch.float32
+    w = 8 if dt == "f64" else 4
+    x = torch.rand((ncol, nlev) if layout == ekat_b200.COL_MAJOR else (nlev, ncol), dtype=tdt, device=dev)
+    out = torch.empty_like(x)
+    alg = 2 * nlev * w * ncol
+    ms = timeit(lambda: adj_diff(x, forward, layout=layout, out=out), flush=alg < (200 << 20))
+    report(kernel="adj_diff", variant=lib().ekat_b200_last_kernel().decode(), dt=dt, ncol=ncol, nlev=nlev,
+           layout="lev" if layout else "col", forward=forward, ms=round(ms, 4), gbs=round(alg / ms / 1e6, 1),
+           frac=round(alg / ms / 1e6 / PEAK, 3))
+
+
 def copy_peak():
     n = 1 << 30
     a = torch.empty(n, dtype=torch.uint8, device=dev)
