@@ -336,7 +336,7 @@ int tridiag_levmajor(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nle
     const int rc = tridiag_tma_shared<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }
-  if (nA == nrhs && !clobber && (variant == 0 || variant == 4 || variant == 5 || variant == 6 || variant == 10 || variant == 11)) {
+  if (nA == nrhs && !clobber && (variant == 0 || variant == 4 || variant == 5 || variant == 6 || variant == 10 || variant == 11 || variant == 12)) {
     const int rc = tridiag_tma<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }

@@ -67,8 +67,12 @@ template bool make_tensor_map_2d<float>(CUtensorMap*, const float*, int64_t, int
 // Shared memory: [ring barriers NS][plane barriers nch] | planes [level][lane] | rings [stage][LB][lane].
 //   FAST : P0 = du -> c',  P1 = x -> y -> solution;            rings dl, d
 //   EXACT: P0 = d  -> d',  P1 = x -> x' -> solution,  P2 = du;  ring  dl
-template <typename R, bool EXACT, int CPT, int RN, int NS, int LBT, bool CM>
-__global__ void __launch_bounds__(32)
+// IO (thomas only): a second warp, one thread of it, issues every copy -- a tensor copy costs its issuing thread ~130
+// cycles and the sweeping warp of the one-warp form issued five per chunk of 8 levels, more than its whole arithmetic
+// in f32. The sweeping warp releases a ring stage as soon as its operands are in registers (ebar) and announces a
+// finished chunk of the solution plane (sbar[k], used once); the io thread refills and stores.
+template <typename R, bool EXACT, int CPT, int RN, int NS, int LBT, bool CM, bool IO = false>
+__global__ void __launch_bounds__(IO ? 64 : 32)
 k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
               const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mx, R* __restrict__ X,
               int64_t ncol, int nlev, int64_t x_stride, int pd) {
@@ -77,14 +81,17 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
   constexpr unsigned CHUNK_BYTES = LB * W * sizeof(R);
   static_assert(LB % RN == 0, "renormalisation interval must divide the chunk");
   extern __shared__ __align__(1024) unsigned char smem_raw[];
-  const int lane = threadIdx.x;
+  static_assert(!(IO && EXACT), "the io warp serves the thomas form only");
+  const int lane = threadIdx.x & 31;
   const int nfull = nlev / LB, ntail = nlev - nfull * LB, nch = nfull + (ntail ? 1 : 0);
 
-  // barriers: ring[NS] | plane[nch] | backward du ring[2*NS] (EXACT)
+  // barriers: ring[NS] | plane[nch] | backward du ring[2*NS] (EXACT) or stage released[NS] + chunk solved[nch] (IO)
   uint64_t* rbar = reinterpret_cast<uint64_t*>(smem_raw);
   uint64_t* pbar = rbar + NS;
   uint64_t* bbar = pbar + nch;
-  const size_t off = ((size_t)(3 * NS + nch) * 8 + 1023) & ~(size_t)1023;  // chunks sit on 1 KB boundaries (swizzle atoms are 512 B)
+  uint64_t* ebar = bbar;       // IO
+  uint64_t* sbar = ebar + NS;  // IO
+  const size_t off = ((size_t)(3 * NS + 2 * nch) * 8 + 1023) & ~(size_t)1023;  // chunks sit on 1 KB boundaries (swizzle atoms are 512 B)
   const size_t plane = (size_t)nch * LB * 32;  // V units
   V* P0 = reinterpret_cast<V*>(smem_raw + off);
   V* P1 = P0 + plane;
@@ -94,14 +101,17 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
   const int c0 = blockIdx.x * W;
   const int row0 = blockIdx.y * nlev;
 
-  if (lane == 0) {
+  if (threadIdx.x == 0) {
     for (int s = 0; s < NS; ++s) mbar_init(&rbar[s], 1);
     for (int k = 0; k < nch; ++k) mbar_init(&pbar[k], 1);
     if (EXACT)
       for (int s = 0; s < 2 * NS; ++s) mbar_init(&bbar[s], 1);
+    if (IO)
+      for (int s = 0; s < NS + nch; ++s) mbar_init(&ebar[s], 1);
     fence_mbar_init();
   }
-  __syncwarp();
+  if (IO) __syncthreads();
+  else __syncwarp();
 
   // L2 policies: every operand is read once (evict-first) except bfb's du, which the back-substitution reads
   // again ~20 us later: it is kept in the 126 MB L2 (evict-last) instead of in a third shared-memory plane,
@@ -131,7 +141,36 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
     mbar_expect_tx(&bbar[s], CHUNK_BYTES);
     load_chunk(RA + (size_t)s * LB * 32, &mdu, nch - 1 - j, &bbar[s], pol_stream);
   };
-  if (lane == 0) {
+  if (IO && threadIdx.x >= 32) {
+    // ------------------------------------------------------------ io warp
+    if (lane != 0) return;
+    const int n0 = pd > NS ? pd : NS;
+    for (int k = 0; k < n0 && k < nch; ++k) {
+      if (k < NS) issue_ring(k);
+      if (k < pd) issue_plane(k);
+    }
+    unsigned eph = 0;
+    for (int k = 0; k < nch; ++k) {
+      const int s = k % NS;
+      mbar_wait(&ebar[s], (eph >> s) & 1u);
+      eph ^= 1u << s;
+      if (k + NS < nch) issue_ring(k + NS);
+      if (k + pd < nch) issue_plane(k + pd);
+    }
+    for (int k = nch - 1; k >= 0; --k) {
+      mbar_wait(&sbar[k], 0u);
+      if (CM) {
+        tma_store_2d(&mx, k * LB, c0, P1 + (size_t)k * LB * 32);
+        tma_store_commit();
+      } else if (k != nfull) {
+        tma_store_2d(&mx, c0, row0 + k * LB, P1 + (size_t)k * LB * 32);
+        tma_store_commit();
+      }
+    }
+    tma_store_wait_read<0>();  // shared memory must outlive the stores' reads
+    return;
+  }
+  if (!IO && lane == 0) {
     const int n0 = pd > NS ? pd : NS;
     for (int k = 0; k < n0 && k < nch; ++k) {
       if (k < NS) issue_ring(k);
@@ -167,6 +206,10 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
       x[u] = ld(p1, u);
       b[u] = EXACT ? ld(p0, u) : ld(rb, u);
       c[u] = EXACT ? ld(rb, u) : ld(p0, u);
+    }
+    if (IO) {  // the stage's operands are in registers: it can be refilled while this chunk is swept
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ebar[s]);
     }
     if (EXACT) {
       R sd[CPT], sx[CPT], su[CPT];
@@ -228,7 +271,7 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
       t_st<R, CPT, LB, CM>(p1, u, lane, o1[u]);
     }
     __syncwarp();  // every lane has read ring stage s
-    if (lane == 0) {
+    if (!IO && lane == 0) {
       if (k + NS < nch) issue_ring(k + NS);
       if (k + pd < nch) issue_plane(k + pd);
     }
@@ -332,7 +375,9 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
       fence_proxy_async();  // generic-proxy writes of this chunk -> visible to the TMA store
     }
     __syncwarp();  // every lane has read its du stage / written its part of the chunk
-    if (lane == 0) {
+    if (IO) {
+      if (lane == 0) mbar_arrive(&sbar[k]);
+    } else if (lane == 0) {
       if (CM) {
         tma_store_2d(&mx, k * LB, c0, P1 + (size_t)k * LB * 32);
         tma_store_commit();
@@ -343,7 +388,7 @@ k_tridiag_tma(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ C
       if (EXACT && jb + 2 * NS < nch) issue_back(jb + 2 * NS);
     }
   }
-  if (lane == 0) tma_store_wait_read<0>();  // shared memory must outlive the stores' reads
+  if (!IO && lane == 0) tma_store_wait_read<0>();  // shared memory must outlive the stores' reads
 }
 
 // ------------------------------------------------------------------------------------------- bfb, x' kept in L2
@@ -681,7 +726,7 @@ k_tridiag_bfb_spill(const __grid_constant__ CUtensorMap mdl, const __grid_consta
 
 // ------------------------------------------------------------------------------------------- host side
 
-template <typename R, bool EXACT, int NS, bool CM>
+template <typename R, bool EXACT, int NS, bool CM, bool IO = false>
 static int launch_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
                       int pd, size_t smem, cudaStream_t stream, const char* name) {
   constexpr int CPT = TmaCfg<R>::CPT, LB = TmaGeom<R, CM>::LB, RN = EXACT ? 1 : TmaGeom<R, CM>::RN, W = 32 * CPT;
@@ -697,11 +742,11 @@ static int launch_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat
          make_tensor_map_2d<R>(&mdu, du, ncol, rows, a_stride, W, LB, 0) && make_tensor_map_2d<R>(&mx, X, ncol, rows, x_stride, W, LB, 0);
   }
   if (!ok) return EKAT_B200_ERR_UNSUPPORTED;
-  auto k = k_tridiag_tma<R, EXACT, CPT, RN, NS, LB, CM>;
+  auto k = k_tridiag_tma<R, EXACT, CPT, RN, NS, LB, CM, IO>;
   int rc = allow_smem(k, smem);
   if (rc) return rc;
   dim3 grid((unsigned)((ncol + W - 1) / W), (unsigned)nmat);
-  k<<<grid, 32, smem, stream>>>(mdl, md, mdu, mx, X, ncol, nlev, x_stride, pd);
+  k<<<grid, IO ? 64 : 32, smem, stream>>>(mdl, md, mdu, mx, X, ncol, nlev, x_stride, pd);
   note_launch(name);
   return check_cuda(cudaGetLastError());
 }
@@ -780,7 +825,7 @@ static int run_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev,
 #undef EKB_SPILL
     }
   }
-  const size_t bars = ((size_t)(12 + nch) * 8 + 1023) & ~(size_t)1023;
+  const size_t bars = ((size_t)(12 + 2 * nch) * 8 + 1023) & ~(size_t)1023;
   const size_t planes = (size_t)2 * nch * chunk;
   const int nrings = 2;
   // ring depth: 4 stages, or 2 if that lets one more CTA share the SM (measured: residency wins over ring depth)
@@ -798,6 +843,10 @@ static int run_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev,
   if (exact)
     return ns == 2 ? launch_tma<R, true, 2, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name)
                    : launch_tma<R, true, 4, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name);
+  if (tu.variant == 12)  // io-warp form: measured slower here (f32 69% against 72%; f64 with one matrix per rhs 76% against
+                         // 78%) -- unlike bfb, whose long chain leaves the sweeping warp no slack; kept for A/B measurements
+    return ns == 2 ? launch_tma<R, false, 2, CM, true>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name)
+                   : launch_tma<R, false, 4, CM, true>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name);
   return ns == 2 ? launch_tma<R, false, 2, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name)
                  : launch_tma<R, false, 4, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name);
 }

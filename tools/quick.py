@@ -1,6 +1,8 @@
-import sys, os; sys.path.insert(0,"tools"); sys.path.insert(0,".")
+import sys; sys.path.insert(0,"tools"); sys.path.insert(0,".")
 import sweep, ekat_b200
-for mb in (0, 24, 48, 64, 96, 128, 192, 256, 512):
-    os.environ["EKAT_B200_SLAB_MB"] = str(mb)
-    print("slab MB", mb, flush=True)
-    sweep.fused_case("f64", 1572864, 128, 128, 10)
+V=[(0,0,0),(0,0,12),(2,0,0),(4,0,0)]
+sweep.tridiag_case("thomas","f32",345600,128, tunings=V)
+sweep.tridiag_case("thomas","f32",3145728,128, tunings=V)
+sweep.tridiag_case("thomas","f32",345600,72, tunings=V)
+sweep.tridiag_case("thomas","f64",345600,128, nA=4, nrhs=4, tunings=V)
+sweep.tridiag_case("thomas","f32",345600,128, layout=ekat_b200.COL_MAJOR, tunings=[(0,0,0),(0,0,12)])
