@@ -44,6 +44,7 @@ def timeit(fn, restore=None, iters=10, flush=False):
         if flush:
             flush_l2()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda._sleep(200_000)  # the host enqueues while the device is busy: the events then bracket the kernel only
         a.record()
         fn()
         b.record()
@@ -111,6 +112,22 @@ def fused_case(dt, ncol, nlev, km2, nrhs, tunings=((0, 0, 0),)):
         lib().ekat_b200_set_tuning(0, 0, 0)
         report(kernel="tridiag_lin_interp", dt=dt, ncol=ncol, nlev=nlev, km2=km2, nrhs=nrhs, tuning=tu, ms=round(ms, 4),
                col_lev_per_s=ncol * nlev / ms * 1e3, gbs=round(alg / ms / 1e6, 1), frac=round(alg / ms / 1e6 / PEAK, 3))
+
+
+def li_lm_case(dt, ncol, km1, km2, nf, tunings=((0, 0, 0),)):
+    from ekat_b200.lin_interp import lin_interp_lm
+    tdt = torch.float64 if dt == "f64" else torch.float32
+    w = 8 if dt == "f64" else 4
+    x1, _, x2 = li_fill(tdt, ncol, km1, km2, 1, device=dev, lev_major=True)
+    y1 = torch.rand((nf, km1, ncol), dtype=tdt, device=dev)
+    y2 = torch.empty((nf, km2, ncol), dtype=tdt, device=dev)
+    alg = (km1 + km2) * (1 + nf) * w * ncol
+    for tu in tunings:
+        lib().ekat_b200_set_tuning(*tu)
+        ms = timeit(lambda: lin_interp_lm(x1, x2, y1, y2))
+        lib().ekat_b200_set_tuning(0, 0, 0)
+        report(kernel="lin_interp_lm", dt=dt, ncol=ncol, km1=km1, km2=km2, nfields=nf, tuning=tu, ms=round(ms, 4),
+               gbs=round(alg / ms / 1e6, 1), frac=round(alg / ms / 1e6 / PEAK, 3))
 
 
 def reduction_case(dt, ncol, nlev, layout=ekat_b200.COL_MAJOR, serialize=True, pack=16):
