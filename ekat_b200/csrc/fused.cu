@@ -141,15 +141,25 @@ int lin_interp_lm(const R* x1, const R* x2, const R* y1, R* y2, int64_t ncol, in
                   cudaStream_t stream);
 
 template <typename R>
+int solve_remap_tma(const R* dl, const R* d, const R* du, const R* Bm, const R* x1, const R* x2, R* Y2, R* X, int64_t ncol,
+                    int nlev, int km2, int nrhs, int64_t pitch, cudaStream_t stream);
+
+template <typename R>
 int tridiag_lin_interp(const R* dl, const R* d, const R* du, const R* B, const R* x1, const R* x2, R* Y2, R* X,
                        int64_t ncol, int nlev, int km2, int nrhs, int64_t pitch, cudaStream_t stream) {
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  // One kernel, every plane of a 16-column tile on chip (fused_tma.cu), whenever the tile fits: nothing but the inputs
+  // and the remapped fields crosses HBM. Tuning variant 3 skips it (A/B against the two-pass path below).
+  if (tuning().variant == 0) {
+    const int rc = solve_remap_tma<R>(dl, d, du, B, x1, x2, Y2, X, ncol, nlev, km2, nrhs, pitch, stream);
+    if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+  }
   // Fast path: the persistent TMA solve (B -> X, out of place) followed by the level-major interpolation (X -> Y2),
   // both at their own HBM roofline. The solutions make one round trip through HBM/L2 between the two; when the
   // caller does not ask for them (X == nullptr) they are staged in Y2 itself, which has their shape when
   // km2 == nlev, and interpolated in place tile by tile. The one-kernel version below keeps them on chip but
   // holds only 16 columns per SM and runs at a fifth of this speed (profiles/).
-  if (tuning().variant == 0 && km2 > 0 && (X != nullptr || km2 == nlev)) {
+  if ((tuning().variant == 0 || tuning().variant == 3) && km2 > 0 && (X != nullptr || km2 == nlev)) {
     R* sol = X ? X : Y2;
     int rc = tridiag_tma_shared_oop<R>(false, const_cast<R*>(dl), const_cast<R*>(d), const_cast<R*>(du), B, sol, ncol, nlev,
                                        nrhs, pitch, pitch, stream);
