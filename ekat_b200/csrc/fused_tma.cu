@@ -500,6 +500,94 @@ k_solve_remap_persist(const __grid_constant__ CUtensorMap mdl, const __grid_cons
   }
 }
 
+// One chunk of LB levels of a solver lane's sweeps over planes [level][TW]; pm, pr, pc, px point at the chunk's first
+// level of the lane's column, nrem = levels left from there. FULL: all LB levels exist (constant offsets, no guards).
+template <typename R, int TW, bool FULL>
+__device__ __forceinline__ void fwd_chunk(const R* pm, const R* pr, R* px, int nrem, R& yprev) {
+  constexpr int LB = kLB;
+  R m[LB], g[LB], x[LB];
+#pragma unroll
+  for (int u = 0; u < LB; ++u) {
+    const int l = FULL ? u : tmin(u, nrem - 1);
+    m[u] = pm[l * TW];
+    g[u] = pr[l * TW];
+    x[u] = px[l * TW];
+  }
+#pragma unroll
+  for (int u = 0; u < LB; ++u) {
+    yprev = f_fma(-m[u], yprev, x[u]);  // forward sweep; the stored value is already divided by the pivot
+    x[u] = yprev * g[u];
+  }
+#pragma unroll
+  for (int u = 0; u < LB; ++u)
+    if (FULL || u < nrem) px[u * TW] = x[u];
+}
+template <typename R, int TW, bool FULL>
+__device__ __forceinline__ void bwd_chunk(const R* pc, R* px, int nrem, R& xv) {
+  constexpr int LB = kLB;
+  R c[LB], y[LB];
+#pragma unroll
+  for (int u = 0; u < LB; ++u) {
+    const int l = FULL ? u : tmin(u, nrem - 1);
+    c[u] = pc[l * TW];
+    y[u] = px[l * TW];
+  }
+#pragma unroll
+  for (int u = LB - 1; u >= 0; --u) {
+    if (FULL || u < nrem) {
+      xv = f_fma(-c[u], xv, y[u]);
+      y[u] = xv;
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < LB; ++u)
+    if (FULL || u < nrem) px[u * TW] = y[u];
+}
+
+// One chunk of LB levels of the factor warp: ratio form of tridiag_tma_shared.cu, in place (dl -> multipliers,
+// d -> reciprocal pivots, du -> c'). pm, pr, pc point at the chunk's first level of the lane's column.
+template <typename R, int TW, bool FULL>
+__device__ __forceinline__ void factor_chunk(R* pm, R* pr, R* pc, int nrem, bool first, R& q1, R& q2, R& cp, R& gp) {
+  constexpr int LB = kLB, RN = TmaCfg<R>::RN;
+  R a[LB], b[LB], c[LB], om[LB], o1[LB], oc[LB];
+#pragma unroll
+  for (int u = 0; u < LB; ++u) {
+    const int l = FULL ? u : tmin(u, nrem - 1);
+    a[u] = pm[l * TW];
+    b[u] = pr[l * TW];
+    c[u] = pc[l * TW];
+  }
+  if (first) a[0] = (R)0;  // dl(0) is never used (ekat_tridiag.hpp:24-27) and may hold anything
+#pragma unroll
+  for (int u = 0; u < LB; ++u) {
+    R q;
+    if (u % RN == 0) q = f_fma(-(a[u] * cp), q2, b[u]);  // renormalised state: q[i-1] == 1
+    else q = f_fma(b[u], q1, -((a[u] * cp) * q2));
+    const R rq = t_rcp(q);
+    const R g = (u % RN == 0) ? rq : q1 * rq;  // q[i-1]/q[i] = 1/pivot[i]
+    om[u] = a[u] * gp;                         // multiplier dl[i]/pivot[i-1]
+    o1[u] = g;
+    oc[u] = (u == nrem - 1) ? (R)0 : c[u] * g;  // du(nrow-1) is never used (:24-27)
+    if ((u + 1) % RN == 0) {
+      q2 = g;
+      q1 = (R)1;
+    } else {
+      q2 = (u % RN == 0) ? (R)1 : q1;
+      q1 = q;
+    }
+    cp = c[u];
+    gp = g;
+  }
+#pragma unroll
+  for (int u = 0; u < LB; ++u) {
+    if (FULL || u < nrem) {
+      pm[u * TW] = om[u];
+      pr[u * TW] = o1[u];
+      pc[u * TW] = oc[u];
+    }
+  }
+}
+
 // The role-split form (the default): no CTA-wide barrier after the prologue. NIW remap warps, NSW solver warps and one
 // factor warp each walk the CTA's tiles at their own pace and hand planes to each other through mbarriers:
 //   remap warps   : wait x1 -> bracket search (the last one out requests x1 of the next tile) -> for every solution f:
@@ -520,7 +608,12 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
   constexpr int WARPS = NIW + NSW + 1, LB = kLB, RN = TmaCfg<R>::RN, TPS = 32 / TW;
   constexpr unsigned B = sizeof(R), ROW = TW * B;
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31;
+  // Role of each warp: 0 .. NIW-1 remap, NIW .. NIW+NSW-1 solver, WARPS-1 factor. A warp issues from scheduler
+  // (warp id % 4); with 10 + 5 + 1 warps the latency-bound warps -- the factor warp and the solvers of the planes that
+  // are released last -- share scheduler 3, the other two solvers sit on scheduler 2 with two remap warps, and the
+  // other eight remap warps fill schedulers 0 and 1, so the recurrences do not queue behind the remap's instructions.
+  const int warp = (NIW == 10 && NSW == 5) ? (int)((0xF987E654DB32CA10ull >> (4 * (tid >> 5))) & 15) : tid >> 5;
   const int lc = lane % TW, sub = lane / TW;
   const int nch = (nlev + LB - 1) / LB;
   // barriers: [0] x1 landed, [1] dl+d+du landed, [2] factor planes free (NSW arrivals), then per rhs: landed[r],
@@ -580,44 +673,9 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
       mbar_wait(&bars[1], par);
       R q1 = (R)1, q2 = (R)0, cp = (R)0, gp = (R)0;
       for (int k = 0; k < nch; ++k) {
-        const int l0 = k * LB;
-        R a[LB], b[LB], c[LB], om[LB], o1[LB], oc[LB];
-#pragma unroll
-        for (int u = 0; u < LB; ++u) {
-          const int l = l0 + u < nlev ? l0 + u : nlev - 1;
-          a[u] = PM[l * TW + lc];
-          b[u] = PR[l * TW + lc];
-          c[u] = PC[l * TW + lc];
-        }
-        if (k == 0) a[0] = (R)0;  // dl(0) is never used (ekat_tridiag.hpp:24-27) and may hold anything
-#pragma unroll
-        for (int u = 0; u < LB; ++u) {
-          R q;
-          if (u % RN == 0) q = f_fma(-(a[u] * cp), q2, b[u]);  // renormalised state: q[i-1] == 1
-          else q = f_fma(b[u], q1, -((a[u] * cp) * q2));
-          const R rq = t_rcp(q);
-          const R g = (u % RN == 0) ? rq : q1 * rq;  // q[i-1]/q[i] = 1/pivot[i]
-          om[u] = a[u] * gp;                         // multiplier dl[i]/pivot[i-1]
-          o1[u] = g;
-          oc[u] = (l0 + u == nlev - 1) ? (R)0 : c[u] * g;  // du(nrow-1) is never used (:24-27)
-          if ((u + 1) % RN == 0) {
-            q2 = g;
-            q1 = (R)1;
-          } else {
-            q2 = (u % RN == 0) ? (R)1 : q1;
-            q1 = q;
-          }
-          cp = c[u];
-          gp = g;
-        }
-#pragma unroll
-        for (int u = 0; u < LB; ++u) {
-          if (l0 + u < nlev) {
-            PM[(l0 + u) * TW + lc] = om[u];
-            PR[(l0 + u) * TW + lc] = o1[u];
-            PC[(l0 + u) * TW + lc] = oc[u];
-          }
-        }
+        const int o = k * LB * TW + lc, nrem = nlev - k * LB;
+        if (nrem >= LB) factor_chunk<R, TW, true>(PM + o, PR + o, PC + o, nrem, k == 0, q1, q2, cp, gp);
+        else factor_chunk<R, TW, false>(PM + o, PR + o, PC + o, nrem, k == 0, q1, q2, cp, gp);
         __syncwarp();
         if (lane == 0) mbar_arrive(&fbar[k]);
       }
@@ -636,44 +694,15 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
           R yprev = (R)0;
           for (int k = 0; k < nch; ++k) {
             mbar_wait(&fbar[k], par);
-            const int l0 = k * LB;
-            R m[LB], g[LB], x[LB];
-#pragma unroll
-            for (int u = 0; u < LB; ++u) {
-              const int l = l0 + u < nlev ? l0 + u : nlev - 1;
-              m[u] = PM[l * TW + lc];
-              g[u] = PR[l * TW + lc];
-              x[u] = px[l * TW];
-            }
-#pragma unroll
-            for (int u = 0; u < LB; ++u) {
-              yprev = f_fma(-m[u], yprev, x[u]);  // forward sweep; the stored value is already divided by the pivot
-              x[u] = yprev * g[u];
-            }
-#pragma unroll
-            for (int u = 0; u < LB; ++u)
-              if (l0 + u < nlev) px[(l0 + u) * TW] = x[u];
+            const int o = k * LB * TW, nrem = nlev - k * LB;
+            if (nrem >= LB) fwd_chunk<R, TW, true>(PM + o + lc, PR + o + lc, px + o, nrem, yprev);
+            else fwd_chunk<R, TW, false>(PM + o + lc, PR + o + lc, px + o, nrem, yprev);
           }
           R xv = (R)0;
           for (int k = nch - 1; k >= 0; --k) {
-            const int l0 = k * LB;
-            R c[LB], y[LB];
-#pragma unroll
-            for (int u = 0; u < LB; ++u) {
-              const int l = l0 + u < nlev ? l0 + u : nlev - 1;
-              c[u] = PC[l * TW + lc];
-              y[u] = px[l * TW];
-            }
-#pragma unroll
-            for (int u = LB - 1; u >= 0; --u) {
-              if (l0 + u < nlev) {
-                xv = f_fma(-c[u], xv, y[u]);
-                y[u] = xv;
-              }
-            }
-#pragma unroll
-            for (int u = 0; u < LB; ++u)
-              if (l0 + u < nlev) px[(l0 + u) * TW] = y[u];
+            const int o = k * LB * TW, nrem = nlev - k * LB;
+            if (nrem >= LB) bwd_chunk<R, TW, true>(PC + o + lc, px + o, nrem, xv);
+            else bwd_chunk<R, TW, false>(PC + o + lc, px + o, nrem, xv);
           }
         }
         __syncwarp();
