@@ -722,8 +722,8 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
       const int64_t gc = c < ncol ? c : ncol - 1;
 #pragma unroll
       for (int t = 0; t < NT; ++t) {
-        const int j = warp * TPS + sub + t * (NIW * TPS);
-        xt[t] = j < km2 ? __ldg(x2 + (size_t)j * pitch + gc) : (R)0;
+        const int j = tmin(warp * TPS + sub + t * (NIW * TPS), km2 - 1);  // surplus slots redo the last target
+        xt[t] = __ldg(x2 + (size_t)j * pitch + gc);
       }
     }
     unsigned par = 0;
@@ -739,20 +739,15 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
       mbar_wait(&bars[0], par);
 #pragma unroll
       for (int t = 0; t < NT; ++t) {
-        const int j = warp * TPS + sub + t * (NIW * TPS);
-        off[t] = 0;
-        dxt[t] = (R)0;
-        dx[t] = (R)1;
-        rc[t] = (R)1;
-        if (j < km2) {
-          const unsigned o = bracket_off<R, LOG2P, ROW>(x1a, nlev, P, xt[t]);
-          const unsigned oph = o == last_off ? o - ROW : o + ROW;  // k1ph, ekat_lin_interp_impl.hpp:119-131
-          const R xa = lds_at(x1a + o, R()), xb = lds_at(x1a + oph, R());
-          off[t] = o;
-          dxt[t] = x_sub(xt[t], xa);
-          dx[t] = x_sub(xb, xa);
-          rc[t] = rcp_refined(dx[t]);
-        }
+        // no branch on j < km2: the seven searches of a thread are independent chains of shared-memory probes and
+        // must be free to interleave (surplus slots hold a copy of the last target and are never stored)
+        const unsigned o = bracket_off<R, LOG2P, ROW>(x1a, nlev, P, xt[t]);
+        const unsigned oph = o == last_off ? o - ROW : o + ROW;  // k1ph, ekat_lin_interp_impl.hpp:119-131
+        const R xa = lds_at(x1a + o, R()), xb = lds_at(x1a + oph, R());
+        off[t] = o;
+        dxt[t] = x_sub(xt[t], xa);
+        dx[t] = x_sub(xb, xa);
+        rc[t] = rcp_refined(dx[t]);
         pin(dxt[t]);  // left to itself the compiler recomputes these per field instead of keeping them
         pin(dx[t]);
         pin(rc[t]);
@@ -775,8 +770,8 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
         const int64_t gc = c < ncol ? c : ncol - 1;
 #pragma unroll
         for (int t = 0; t < NT; ++t) {
-          const int j = warp * TPS + sub + t * (NIW * TPS);
-          xt[t] = j < km2 ? __ldg(x2 + (size_t)j * pitch + gc) : (R)0;
+          const int j = tmin(warp * TPS + sub + t * (NIW * TPS), km2 - 1);
+          xt[t] = __ldg(x2 + (size_t)j * pitch + gc);
         }
       }
 
@@ -793,18 +788,29 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
         const unsigned y1a = smem_u32(PX + (size_t)f * plane) + (unsigned)lc * B;
         R* gy = gy0;  // row (f, j0) of this thread's column; the targets of a thread are NIW * TPS rows apart
         gy0 += (size_t)km2 * pitch;
+        bool bad = false;
 #pragma unroll
-        for (int t = 0; t < NT; ++t, gy += tstride) {
-          const int j = j0 + t * (NIW * TPS);
-          if (j < km2) {
+        for (int t = 0; t < NT; ++t) {
+          const unsigned o = off[t];
+          const unsigned oph = o == last_off ? o - ROW : o + ROW;
+          const R ya = lds_at(y1a + o, R()), yb = lds_at(y1a + oph, R());
+          R v = x_sub(yb, ya);                   // ekat_lin_interp_impl.hpp:153
+          v = x_mul(v, dxt[t]);                  // :154
+          v = div_spec(v, dx[t], rc[t], bad);    // :155 (fast-path quotient; `bad` records operands it is not proven for)
+          v = x_add(v, ya);                      // :156
+          if (live && j0 + t * (NIW * TPS) < km2) st_stream(gy + t * tstride, v);
+        }
+        if (__builtin_expect(bad, 0)) {  // rare operands: the same statements with the full-range division
+#pragma unroll
+          for (int t = 0; t < NT; ++t) {
             const unsigned o = off[t];
             const unsigned oph = o == last_off ? o - ROW : o + ROW;
             const R ya = lds_at(y1a + o, R()), yb = lds_at(y1a + oph, R());
-            R v = x_sub(yb, ya);                 // ekat_lin_interp_impl.hpp:153
-            v = x_mul(v, dxt[t]);                // :154
-            v = div_given_rcp(v, dx[t], rc[t]);  // :155
-            v = x_add(v, ya);                    // :156
-            if (live) st_stream(gy, v);
+            R v = x_sub(yb, ya);
+            v = x_mul(v, dxt[t]);
+            v = x_div_full(v, dx[t]);
+            v = x_add(v, ya);
+            if (live && j0 + t * (NIW * TPS) < km2) st_stream(gy + t * tstride, v);
           }
         }
         __syncwarp();
