@@ -362,17 +362,21 @@ def run_extras(torch, dev, peak):
         alg = (2 * km1 + 2 * 128) * 8 * ncol
         out.append({"case": label + f" ({ncol} columns)", "kernel": lib().ekat_b200_last_kernel().decode(), "ms": ms,
                     "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak, "col_lev_per_s": ncol * 128 / ms * 1e3})
-    # config 4 whole: 10-rhs solve + remap of the 10 solutions (persistent TMA solve, then level-major LinInterp)
+    # config 4 whole: 10-rhs solve + remap of the 10 solutions, one kernel (fused_tma.cu), f64 and f32
     from ekat_b200.lin_interp import tridiag_lin_interp
     ncol, nrhs = 1572864, 10
-    dl, d, du, Bm = T.fill(torch.float64, ncol, 128, 1, nrhs, device=dev)
-    x1, _, x2 = li_fill(torch.float64, ncol, 128, 128, 1, device=dev, lev_major=True)
-    Y2 = torch.zeros((nrhs, 128, ncol), dtype=torch.float64, device=dev)
-    ms = timed(lambda: tridiag_lin_interp(dl[0], d[0], du[0], Bm, x1, x2, Y2))
-    alg = (3 + nrhs + 2 + nrhs) * 128 * 8 * ncol
-    out.append({"case": "config 4, 10-rhs thomas + LinInterp 128->128 of the 10 solutions (25,600 B/column algorithmic)",
-                "kernel": "tridiag_tma_shared<f64,thomas> + " + lib().ekat_b200_last_kernel().decode(), "ms": ms,
-                "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak, "col_lev_per_s": ncol * 128 / ms * 1e3})
+    for tdt, w in ((torch.float64, 8), (torch.float32, 4)):
+        dl, d, du, Bm = T.fill(tdt, ncol, 128, 1, nrhs, device=dev)
+        x1, _, x2 = li_fill(tdt, ncol, 128, 128, 1, device=dev, lev_major=True)
+        Y2 = torch.zeros((nrhs, 128, ncol), dtype=tdt, device=dev)
+        ms = timed(lambda: tridiag_lin_interp(dl[0], d[0], du[0], Bm, x1, x2, Y2))
+        alg = (3 + nrhs + 2 + nrhs) * 128 * w * ncol
+        kern = lib().ekat_b200_last_kernel().decode()
+        if not kern.startswith("solve_remap"):
+            kern = "tridiag_tma_shared + " + kern
+        out.append({"case": f"config 4, 10-rhs thomas + LinInterp 128->128 of the 10 solutions, f{8 * w} ({alg // ncol:,} B/column algorithmic)",
+                    "kernel": kern, "ms": ms, "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak,
+                    "col_lev_per_s": ncol * 128 / ms * 1e3})
     del dl, d, du, Bm, x1, x2, Y2
     torch.cuda.empty_cache()
     # ReductionUtils::view_reduction and the layout marshalling, config 5 shard size

@@ -1,29 +1,30 @@
 // fused_tma.cu -- BASELINE config 4 in ONE kernel: the shared-matrix Thomas solve of nrhs right-hand sides followed
-// by the vertical remap of the nrhs solutions, a tile of 16 columns per CTA, nothing but the inputs and the remapped
-// fields crossing HBM (25,600 B per column at 128 levels x 10 right-hand sides, f64).
+// by the vertical remap of the nrhs solutions, a tile of 16 columns kept on chip, nothing but the inputs and the
+// remapped fields crossing HBM (25,600 B per column at 128 levels x 10 right-hand sides, f64).
 //
 // Replaces, back to back, the per-column loops around ekat::tridiag::thomas(team, dl, d, du, X[nrow][nrhs])
 // (reference src/algorithm/ekat_tridiag.hpp:177-214, :323-334) and LinInterp::setup / lin_interp on each solution
 // (src/algorithm/ekat_lin_interp_impl.hpp:89-186). Level-major operands (columns fastest).
 //
 // Why this shape. The two-pass path (tridiag_tma_shared.cu, then lin_interp_lm.cu) sends the solutions through HBM
-// once in each direction: 45.5 KB per column for 25.6 KB algorithmic. Here a CTA owns 16 columns and keeps every
-// plane [level][16 columns] of its tile on chip -- dl -> multipliers, d -> reciprocal pivots, du -> c', the nrhs
-// right-hand sides -> solutions, and the source coordinates x1: 14 planes of 16 KB at 128 levels f64 = 224 KB, the
-// whole shared memory of an SM. There is no room to prefetch the next tile, so the tile's own phases are overlapped
-// with its copies instead: every plane is requested by one TMA tensor copy at the very start (224 KB in flight per
-// SM), and the phases run in the order their operands land:
-//   1. all 8 warps: bracket search of the 128 x 16 targets as soon as x1 is there (x2 straight from global); a thread
-//      owns 8 (target, column) pairs and keeps bracket, x2 - x1[k1], the interval and its refined reciprocal in
-//      registers for every field (lin_interp_lm.cu);
-//   2. warp 7 factorises (continuant / ratio form, tridiag_tma.cu) chunk by chunk as soon as dl, d, du are there,
-//      warps 0-4 follow it with the forward sweeps of two right-hand sides each (lane = (rhs parity, column)) as their
-//      planes land, then run the back-substitutions;
-//   3. all 8 warps interpolate the nrhs solutions where they lie (conflict-free gathers: a lane only touches its own
-//      column's banks) and write the fields as coalesced 128-byte row segments.
-// The next CTA of the SM starts while this one's stores drain. Arithmetic: thomas as in tridiag_tma_shared.cu
-// (<= 3e-15 relative to the reference), LinInterp the reference's four statements in order with IEEE division
-// (div_given_rcp == __ddiv_rn) -- bit-identical to ekat::LinInterp applied to the same solutions.
+// once in each direction: 45.5 KB per column for 25.6 KB algorithmic. Here a persistent CTA (one per SM) keeps every
+// plane [level][16 columns] of its current tile in shared memory -- dl -> multipliers, d -> reciprocal pivots,
+// du -> c', the nrhs right-hand sides -> solutions, and the source coordinates x1: 14 planes of 16 KB at 128 levels
+// f64 = 224 KB, all an SM has. There is no room for a second tile, so the pipeline runs plane by plane instead: each
+// plane is handed to the next tile the moment the current tile is done with it (see k_solve_remap_roles).
+//
+// Arithmetic: thomas as in tridiag_tma_shared.cu (ratio form, <= 3e-15 relative to the reference); LinInterp the
+// reference's four statements in order with IEEE division (div_spec fast path == __ddiv_rn, full-range redo
+// otherwise) -- bit-identical to ekat::LinInterp applied to the same solutions.
+//
+// What was tried on the way (B200, f64, 1,572,864 x 128 -> 128, 10 rhs; two-pass = 14.7 ms):
+//   one CTA per tile, three CTA-wide phases (search | factor + sweeps | remap)          13.6 ms
+//   the same, 8-column tiles so that two CTAs share an SM                               14.6 ms
+//   persistent CTA, CTA-wide phases, next tile's copies issued as planes free up        13.3 ms
+//   role-split warps (this file)                                                        12.7 ms
+//   + full-range division out of line, full-chunk fast paths, warp roles grouped by scheduler   10.8 ms
+//   + branch-free search / remap so that a thread's seven targets interleave             9.8 ms
+//   (- software-pipelined sweeps 10.6 ms; - L2 prefetch of the next tile's planes 10.5-13 ms: both dropped)
 #include <cuda.h>
 
 
@@ -35,470 +36,6 @@ namespace ekb {
 // An empty asm the value passes through: the compiler can no longer see where it came from and keeps it in a register.
 __device__ __forceinline__ void pin(double& v) { asm volatile("" : "+d"(v)); }
 __device__ __forceinline__ void pin(float& v) { asm volatile("" : "+f"(v)); }
-
-// TW columns per tile, WARPS warps per CTA, NT targets per thread (km2 <= NT * WARPS * 32 / TW), MINB CTAs per SM the
-// register budget is set for. Two shapes are used: 16 columns x 16 warps (one CTA per SM) and 8 columns x 8 warps (two
-// CTAs per SM when the tile is small enough: one tile's sweeps then run under the other's copies).
-template <typename R, int LOG2P, int TW, int WARPS, int NT, int MINB>
-__global__ void __launch_bounds__(32 * WARPS, MINB)
-k_solve_remap(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
-              const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mb,
-              const __grid_constant__ CUtensorMap mx1, const R* __restrict__ x2, R* __restrict__ Y2, R* __restrict__ X,
-              int64_t ncol, int nlev, int km2, int nrhs, int64_t pitch, int P) {
-  constexpr int kFtWarps = WARPS, LB = kLB, RN = TmaCfg<R>::RN, TPS = 32 / TW;
-  constexpr unsigned B = sizeof(R), ROW = TW * B;
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int lc = lane % TW, sub = lane / TW;
-  const int nch = (nlev + LB - 1) / LB;
-  // barriers: [0] x1, [1] dl+d+du, [2 + r] right-hand side r, [2 + nrhs + k] factor chunk k done
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);
-  const size_t bar_bytes = ((size_t)(2 + nrhs + nch) * 8 + (size_t)nrhs * 4 + 127) & ~(size_t)127;
-  const size_t plane = (((size_t)nlev * ROW + 127) & ~(size_t)127) / B;  // elements per plane
-  R* PM = reinterpret_cast<R*>(smem_raw + bar_bytes);  // dl -> multipliers
-  R* PR = PM + plane;                                  // d  -> reciprocal pivots
-  R* PC = PR + plane;                                  // du -> c'
-  R* PX1 = PC + plane;                                 // x1
-  R* PX = PX1 + plane;                                 // [nrhs] right-hand sides -> solutions
-
-  const int c0 = blockIdx.x * TW;
-  const int64_t col = (int64_t)c0 + lc;
-  const bool live = col < ncol;
-  const int64_t gcol = live ? col : ncol - 1;
-  const unsigned plane_bytes = (unsigned)nlev * ROW;
-
-  if (tid == 0) {
-    for (int i = 0; i < 2 + nrhs + nch; ++i) mbar_init(&bars[i], 1);
-    fence_mbar_init();
-    mbar_expect_tx(&bars[0], plane_bytes);
-    tma_load_2d(PX1, &mx1, c0, 0, &bars[0]);
-    mbar_expect_tx(&bars[1], 3u * plane_bytes);
-    tma_load_2d(PM, &mdl, c0, 0, &bars[1]);
-    tma_load_2d(PR, &md, c0, 0, &bars[1]);
-    tma_load_2d(PC, &mdu, c0, 0, &bars[1]);
-  }
-  __syncthreads();
-  if (warp == kFtWarps - 2 && lane == 0) {  // the right-hand sides, in the order the solver warps want them
-    for (int r = 0; r < nrhs; ++r) {
-      mbar_expect_tx(&bars[2 + r], plane_bytes);
-      tma_load_2d(PX + (size_t)r * plane, &mb, c0, r * nlev, &bars[2 + r]);
-    }
-  }
-
-  // ---------------------------------------------------------------- 1. brackets (all warps)
-  const unsigned x1a = smem_u32(PX1) + (unsigned)lc * B;
-  const unsigned last_off = (unsigned)(nlev - 1) * ROW;
-  unsigned off[NT];
-  R dxt[NT], dx[NT], rc[NT];
-  mbar_wait(&bars[0], 0u);
-#pragma unroll
-  for (int t = 0; t < NT; ++t) {
-    const int j = warp * TPS + sub + t * (kFtWarps * TPS);
-    off[t] = 0;
-    dxt[t] = (R)0;
-    dx[t] = (R)1;
-    rc[t] = (R)1;
-    if (j < km2) {
-      const R xt = __ldg(x2 + (size_t)j * pitch + gcol);
-      const unsigned o = bracket_off<R, LOG2P, ROW>(x1a, nlev, P, xt);
-      const unsigned oph = o == last_off ? o - ROW : o + ROW;  // k1ph, ekat_lin_interp_impl.hpp:119-131
-      const R xa = lds_at(x1a + o, R()), xb = lds_at(x1a + oph, R());
-      off[t] = o;
-      dxt[t] = x_sub(xt, xa);
-      dx[t] = x_sub(xb, xa);
-      rc[t] = rcp_refined(dx[t]);
-    }
-  }
-
-  uint64_t* fbar = bars + 2 + nrhs;
-  if (warp == kFtWarps - 1) {
-    // -------------------------------------------------------------- 2a. factor warp (both half-warps compute the
-    // same 16 columns and write the same values): ratio form of tridiag_tma_shared.cu, 8 levels at a time
-    mbar_wait(&bars[1], 0u);
-    R q1 = (R)1, q2 = (R)0, cp = (R)0, gp = (R)0;
-    for (int k = 0; k < nch; ++k) {
-      const int l0 = k * LB;
-      R a[LB], b[LB], c[LB], om[LB], o1[LB], oc[LB];
-#pragma unroll
-      for (int u = 0; u < LB; ++u) {
-        const int l = l0 + u < nlev ? l0 + u : nlev - 1;
-        a[u] = PM[l * TW + lc];
-        b[u] = PR[l * TW + lc];
-        c[u] = PC[l * TW + lc];
-      }
-      if (k == 0) a[0] = (R)0;  // dl(0) is never used (ekat_tridiag.hpp:24-27) and may hold anything
-#pragma unroll
-      for (int u = 0; u < LB; ++u) {
-        R q;
-        if (u % RN == 0) q = f_fma(-(a[u] * cp), q2, b[u]);  // renormalised state: q[i-1] == 1
-        else q = f_fma(b[u], q1, -((a[u] * cp) * q2));
-        const R rq = t_rcp(q);
-        const R g = (u % RN == 0) ? rq : q1 * rq;  // q[i-1]/q[i] = 1/pivot[i]
-        om[u] = a[u] * gp;                         // multiplier dl[i]/pivot[i-1]
-        o1[u] = g;
-        oc[u] = (l0 + u == nlev - 1) ? (R)0 : c[u] * g;  // du(nrow-1) is never used (:24-27)
-        if ((u + 1) % RN == 0) {
-          q2 = g;
-          q1 = (R)1;
-        } else {
-          q2 = (u % RN == 0) ? (R)1 : q1;
-          q1 = q;
-        }
-        cp = c[u];
-        gp = g;
-      }
-#pragma unroll
-      for (int u = 0; u < LB; ++u) {
-        if (l0 + u < nlev) {
-          PM[(l0 + u) * TW + lc] = om[u];
-          PR[(l0 + u) * TW + lc] = o1[u];
-          PC[(l0 + u) * TW + lc] = oc[u];
-        }
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&fbar[k]);
-    }
-  }
-  constexpr int NSW = WARPS - 3 < 5 ? WARPS - 3 : 5;  // solver warps (the last three warps have other duties first)
-  if (warp < NSW) {
-    // -------------------------------------------------------------- 2b. solver warps: lane = (rhs within the warp, column)
-    for (int r = warp * TPS + sub; r < nrhs; r += NSW * TPS) {
-      R* px = PX + (size_t)r * plane + lc;
-      mbar_wait(&bars[2 + r], 0u);
-      R yprev = (R)0;
-      for (int k = 0; k < nch; ++k) {
-        mbar_wait(&fbar[k], 0u);
-        const int l0 = k * LB;
-        R m[LB], g[LB], x[LB];
-#pragma unroll
-        for (int u = 0; u < LB; ++u) {
-          const int l = l0 + u < nlev ? l0 + u : nlev - 1;
-          m[u] = PM[l * TW + lc];
-          g[u] = PR[l * TW + lc];
-          x[u] = px[l * TW];
-        }
-#pragma unroll
-        for (int u = 0; u < LB; ++u) {
-          yprev = f_fma(-m[u], yprev, x[u]);  // forward sweep; the stored value is already divided by the pivot
-          x[u] = yprev * g[u];
-        }
-#pragma unroll
-        for (int u = 0; u < LB; ++u)
-          if (l0 + u < nlev) px[(l0 + u) * TW] = x[u];
-      }
-      R xv = (R)0;
-      for (int k = nch - 1; k >= 0; --k) {
-        const int l0 = k * LB;
-        R c[LB], y[LB];
-#pragma unroll
-        for (int u = 0; u < LB; ++u) {
-          const int l = l0 + u < nlev ? l0 + u : nlev - 1;
-          c[u] = PC[l * TW + lc];
-          y[u] = px[l * TW];
-        }
-#pragma unroll
-        for (int u = LB - 1; u >= 0; --u) {
-          if (l0 + u < nlev) {
-            xv = f_fma(-c[u], xv, y[u]);
-            y[u] = xv;
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < LB; ++u)
-          if (l0 + u < nlev) px[(l0 + u) * TW] = y[u];
-      }
-    }
-  }
-  __syncthreads();  // every solution plane is complete
-
-  // ---------------------------------------------------------------- (optional) the solutions themselves
-  if (X != nullptr) {
-    for (int r = 0; r < nrhs; ++r) {
-      const R* px = PX + (size_t)r * plane + lc;
-      R* gx = X + ((size_t)r * nlev) * pitch + col;
-      for (int l = warp * TPS + sub; l < nlev; l += kFtWarps * TPS)
-        if (live) st_stream(gx + (size_t)l * pitch, px[l * TW]);
-    }
-  }
-
-  // ---------------------------------------------------------------- 3. remap of every solution (all warps)
-  for (int f = 0; f < nrhs; ++f) {
-    const unsigned y1a = smem_u32(PX + (size_t)f * plane) + (unsigned)lc * B;
-    R* gy = Y2 + ((size_t)f * km2) * pitch + col;
-#pragma unroll
-    for (int t = 0; t < NT; ++t) {
-      const int j = warp * TPS + sub + t * (kFtWarps * TPS);
-      if (j < km2) {
-        const unsigned o = off[t];
-        const unsigned oph = o == last_off ? o - ROW : o + ROW;
-        const R ya = lds_at(y1a + o, R()), yb = lds_at(y1a + oph, R());
-        R v = x_sub(yb, ya);                 // ekat_lin_interp_impl.hpp:153
-        v = x_mul(v, dxt[t]);                // :154
-        v = div_given_rcp(v, dx[t], rc[t]);  // :155
-        v = x_add(v, ya);                    // :156
-        if (live) st_stream(gy + (size_t)j * pitch, v);
-      }
-    }
-  }
-}
-
-// The persistent form: one CTA per SM walks the tiles grid-stride and, having no room for a second tile, re-uses each
-// plane for the next tile the moment the current tile is done with it:
-//   x1 and dl, d, du of tile i+1 are requested at the barrier that ends the sweeps of tile i, the factor warp factorises
-//   tile i+1 as soon as it has finished its share of the remap of tile i, and right-hand side r of tile i+1 is requested
-//   by whichever warp is the last to finish remapping solution r of tile i (a counter in shared memory).
-// So the copies of tile i+1 and the stores of tile i share the remap phase, and only the bracket search and the sweeps
-// run with HBM idle. x2 of the next tile is fetched into registers ahead of the remap.
-template <typename R, int LOG2P, int TW, int WARPS, int NT>
-__global__ void __launch_bounds__(32 * WARPS, 1)
-k_solve_remap_persist(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
-                      const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mb,
-                      const __grid_constant__ CUtensorMap mx1, const R* __restrict__ x2, R* __restrict__ Y2,
-                      R* __restrict__ X, int64_t ncol, int nlev, int km2, int nrhs, int64_t pitch, int P, int ntiles) {
-  constexpr int LB = kLB, RN = TmaCfg<R>::RN, TPS = 32 / TW;
-  constexpr unsigned B = sizeof(R), ROW = TW * B;
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int lc = lane % TW, sub = lane / TW;
-  const int nch = (nlev + LB - 1) / LB;
-  // barriers: [0] x1, [1] dl+d+du, [2 + r] right-hand side r, [2 + nrhs + k] factor chunk k done; then nrhs counters
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);
-  int* cnt = reinterpret_cast<int*>(bars + 2 + nrhs + nch);
-  const size_t bar_bytes = ((size_t)(2 + nrhs + nch) * 8 + (size_t)nrhs * 4 + 127) & ~(size_t)127;
-  const size_t plane = (((size_t)nlev * ROW + 127) & ~(size_t)127) / B;  // elements per plane
-  R* PM = reinterpret_cast<R*>(smem_raw + bar_bytes);  // dl -> multipliers
-  R* PR = PM + plane;                                  // d  -> reciprocal pivots
-  R* PC = PR + plane;                                  // du -> c'
-  R* PX1 = PC + plane;                                 // x1
-  R* PX = PX1 + plane;                                 // [nrhs] right-hand sides -> solutions
-  const unsigned plane_bytes = (unsigned)nlev * ROW;
-  uint64_t* fbar = bars + 2 + nrhs;
-
-  int tile = blockIdx.x;  // grid <= ntiles
-  if (tid == 0) {
-    for (int i = 0; i < 2 + nrhs + nch; ++i) mbar_init(&bars[i], 1);
-    for (int r = 0; r < nrhs; ++r) cnt[r] = 0;
-    fence_mbar_init();
-    mbar_expect_tx(&bars[0], plane_bytes);
-    tma_load_2d(PX1, &mx1, tile * TW, 0, &bars[0]);
-    mbar_expect_tx(&bars[1], 3u * plane_bytes);
-    tma_load_2d(PM, &mdl, tile * TW, 0, &bars[1]);
-    tma_load_2d(PR, &md, tile * TW, 0, &bars[1]);
-    tma_load_2d(PC, &mdu, tile * TW, 0, &bars[1]);
-  }
-  __syncthreads();
-  if (warp == WARPS - 2 && lane == 0) {
-    for (int r = 0; r < nrhs; ++r) {
-      mbar_expect_tx(&bars[2 + r], plane_bytes);
-      tma_load_2d(PX + (size_t)r * plane, &mb, tile * TW, r * nlev, &bars[2 + r]);
-    }
-  }
-  const unsigned x1a = smem_u32(PX1) + (unsigned)lc * B;
-  const unsigned last_off = (unsigned)(nlev - 1) * ROW;
-  R xt[NT];
-  {
-    const int64_t c = (int64_t)tile * TW + lc;
-    const int64_t gc = c < ncol ? c : ncol - 1;
-#pragma unroll
-    for (int t = 0; t < NT; ++t) {
-      const int j = warp * TPS + sub + t * (WARPS * TPS);
-      xt[t] = j < km2 ? __ldg(x2 + (size_t)j * pitch + gc) : (R)0;
-    }
-  }
-
-  for (unsigned par = 0; tile < ntiles; tile += gridDim.x, par ^= 1u) {
-    const int c0 = tile * TW;
-    const int64_t col = (int64_t)c0 + lc;
-    const bool live = col < ncol;
-    const int next = tile + (int)gridDim.x;
-    const bool has_next = next < ntiles;
-
-    if (warp == WARPS - 1) {
-      // ------------------------------------------------------------ factor warp (both half-warps compute the same
-      // columns and write the same values): ratio form of tridiag_tma_shared.cu, 8 levels at a time
-      mbar_wait(&bars[1], par);
-      R q1 = (R)1, q2 = (R)0, cp = (R)0, gp = (R)0;
-      for (int k = 0; k < nch; ++k) {
-        const int l0 = k * LB;
-        R a[LB], b[LB], c[LB], om[LB], o1[LB], oc[LB];
-#pragma unroll
-        for (int u = 0; u < LB; ++u) {
-          const int l = l0 + u < nlev ? l0 + u : nlev - 1;
-          a[u] = PM[l * TW + lc];
-          b[u] = PR[l * TW + lc];
-          c[u] = PC[l * TW + lc];
-        }
-        if (k == 0) a[0] = (R)0;  // dl(0) is never used (ekat_tridiag.hpp:24-27) and may hold anything
-#pragma unroll
-        for (int u = 0; u < LB; ++u) {
-          R q;
-          if (u % RN == 0) q = f_fma(-(a[u] * cp), q2, b[u]);  // renormalised state: q[i-1] == 1
-          else q = f_fma(b[u], q1, -((a[u] * cp) * q2));
-          const R rq = t_rcp(q);
-          const R g = (u % RN == 0) ? rq : q1 * rq;  // q[i-1]/q[i] = 1/pivot[i]
-          om[u] = a[u] * gp;                         // multiplier dl[i]/pivot[i-1]
-          o1[u] = g;
-          oc[u] = (l0 + u == nlev - 1) ? (R)0 : c[u] * g;  // du(nrow-1) is never used (:24-27)
-          if ((u + 1) % RN == 0) {
-            q2 = g;
-            q1 = (R)1;
-          } else {
-            q2 = (u % RN == 0) ? (R)1 : q1;
-            q1 = q;
-          }
-          cp = c[u];
-          gp = g;
-        }
-#pragma unroll
-        for (int u = 0; u < LB; ++u) {
-          if (l0 + u < nlev) {
-            PM[(l0 + u) * TW + lc] = om[u];
-            PR[(l0 + u) * TW + lc] = o1[u];
-            PC[(l0 + u) * TW + lc] = oc[u];
-          }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&fbar[k]);
-      }
-    }
-
-    // -------------------------------------------------------------- brackets (all warps)
-    unsigned off[NT];
-    R dxt[NT], dx[NT], rc[NT];
-    mbar_wait(&bars[0], par);
-#pragma unroll
-    for (int t = 0; t < NT; ++t) {
-      const int j = warp * TPS + sub + t * (WARPS * TPS);
-      off[t] = 0;
-      dxt[t] = (R)0;
-      dx[t] = (R)1;
-      rc[t] = (R)1;
-      if (j < km2) {
-        const unsigned o = bracket_off<R, LOG2P, ROW>(x1a, nlev, P, xt[t]);
-        const unsigned oph = o == last_off ? o - ROW : o + ROW;  // k1ph, ekat_lin_interp_impl.hpp:119-131
-        const R xa = lds_at(x1a + o, R()), xb = lds_at(x1a + oph, R());
-        off[t] = o;
-        dxt[t] = x_sub(xt[t], xa);
-        dx[t] = x_sub(xb, xa);
-        rc[t] = rcp_refined(dx[t]);
-      }
-    }
-
-    constexpr int NSW = WARPS - 3 < 5 ? WARPS - 3 : 5;  // solver warps
-    if (warp < NSW) {
-      // ------------------------------------------------------------ solver warps: lane = (rhs within the warp, column)
-      for (int r = warp * TPS + sub; r < nrhs; r += NSW * TPS) {
-        R* px = PX + (size_t)r * plane + lc;
-        mbar_wait(&bars[2 + r], par);
-        R yprev = (R)0;
-        for (int k = 0; k < nch; ++k) {
-          mbar_wait(&fbar[k], par);
-          const int l0 = k * LB;
-          R m[LB], g[LB], x[LB];
-#pragma unroll
-          for (int u = 0; u < LB; ++u) {
-            const int l = l0 + u < nlev ? l0 + u : nlev - 1;
-            m[u] = PM[l * TW + lc];
-            g[u] = PR[l * TW + lc];
-            x[u] = px[l * TW];
-          }
-#pragma unroll
-          for (int u = 0; u < LB; ++u) {
-            yprev = f_fma(-m[u], yprev, x[u]);  // forward sweep; the stored value is already divided by the pivot
-            x[u] = yprev * g[u];
-          }
-#pragma unroll
-          for (int u = 0; u < LB; ++u)
-            if (l0 + u < nlev) px[(l0 + u) * TW] = x[u];
-        }
-        R xv = (R)0;
-        for (int k = nch - 1; k >= 0; --k) {
-          const int l0 = k * LB;
-          R c[LB], y[LB];
-#pragma unroll
-          for (int u = 0; u < LB; ++u) {
-            const int l = l0 + u < nlev ? l0 + u : nlev - 1;
-            c[u] = PC[l * TW + lc];
-            y[u] = px[l * TW];
-          }
-#pragma unroll
-          for (int u = LB - 1; u >= 0; --u) {
-            if (l0 + u < nlev) {
-              xv = f_fma(-c[u], xv, y[u]);
-              y[u] = xv;
-            }
-          }
-#pragma unroll
-          for (int u = 0; u < LB; ++u)
-            if (l0 + u < nlev) px[(l0 + u) * TW] = y[u];
-        }
-      }
-    }
-    __syncthreads();  // every solution plane is complete; x1 and the factor planes are free
-
-    if (has_next) {
-      if (tid == 0) {
-        fence_proxy_async();
-        mbar_expect_tx(&bars[0], plane_bytes);
-        tma_load_2d(PX1, &mx1, next * TW, 0, &bars[0]);
-        mbar_expect_tx(&bars[1], 3u * plane_bytes);
-        tma_load_2d(PM, &mdl, next * TW, 0, &bars[1]);
-        tma_load_2d(PR, &md, next * TW, 0, &bars[1]);
-        tma_load_2d(PC, &mdu, next * TW, 0, &bars[1]);
-      }
-      const int64_t c = (int64_t)next * TW + lc;
-      const int64_t gc = c < ncol ? c : ncol - 1;
-#pragma unroll
-      for (int t = 0; t < NT; ++t) {
-        const int j = warp * TPS + sub + t * (WARPS * TPS);
-        xt[t] = j < km2 ? __ldg(x2 + (size_t)j * pitch + gc) : (R)0;
-      }
-    }
-
-    // -------------------------------------------------------------- (optional) the solutions themselves
-    if (X != nullptr) {
-      for (int r = 0; r < nrhs; ++r) {
-        const R* px = PX + (size_t)r * plane + lc;
-        R* gx = X + ((size_t)r * nlev) * pitch + col;
-        for (int l = warp * TPS + sub; l < nlev; l += WARPS * TPS)
-          if (live) st_stream(gx + (size_t)l * pitch, px[l * TW]);
-      }
-    }
-
-    // -------------------------------------------------------------- remap of every solution (all warps)
-    for (int f = 0; f < nrhs; ++f) {
-      const unsigned y1a = smem_u32(PX + (size_t)f * plane) + (unsigned)lc * B;
-      R* gy = Y2 + ((size_t)f * km2) * pitch + col;
-#pragma unroll
-      for (int t = 0; t < NT; ++t) {
-        const int j = warp * TPS + sub + t * (WARPS * TPS);
-        if (j < km2) {
-          const unsigned o = off[t];
-          const unsigned oph = o == last_off ? o - ROW : o + ROW;
-          const R ya = lds_at(y1a + o, R()), yb = lds_at(y1a + oph, R());
-          R v = x_sub(yb, ya);                 // ekat_lin_interp_impl.hpp:153
-          v = x_mul(v, dxt[t]);                // :154
-          v = div_given_rcp(v, dx[t], rc[t]);  // :155
-          v = x_add(v, ya);                    // :156
-          if (live) st_stream(gy + (size_t)j * pitch, v);
-        }
-      }
-      __syncwarp();
-      if (lane == 0) {  // the last warp to leave solution f asks for right-hand side f of the next tile in its place
-        __threadfence_block();
-        if (atomicAdd(&cnt[f], 1) == WARPS - 1) {
-          cnt[f] = 0;
-          if (has_next) {
-            __threadfence_block();
-            fence_proxy_async();
-            mbar_expect_tx(&bars[2 + f], plane_bytes);
-            tma_load_2d(PX + (size_t)f * plane, &mb, next * TW, f * nlev, &bars[2 + f]);
-          }
-        }
-      }
-    }
-  }
-}
 
 // One chunk of LB levels of a solver lane's sweeps over planes [level][TW]; pm, pr, pc, px point at the chunk's first
 // level of the lane's column, nrem = levels left from there. FULL: all LB levels exist (constant offsets, no guards).
@@ -831,12 +368,14 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
   }
 }
 
-// Returns EKAT_B200_ERR_UNSUPPORTED when the tile does not fit on chip or the operands do not meet TMA's requirements;
-// the caller then takes the two-pass path.
-template <typename R, int TW, int WARPS, int NT, int MINB>
+constexpr int kFtRemapWarps = 10, kFtSolverWarps = 5;  // + 1 factor warp = 512 threads
+
+template <typename R, int TW>
 static int launch_solve_remap(const R* dl, const R* d, const R* du, const R* Bm, const R* x1, const R* x2, R* Y2, R* X,
                               int64_t ncol, int nlev, int km2, int nrhs, int64_t pitch, size_t smem, cudaStream_t stream) {
-  constexpr int RNT = (128 + (WARPS - 6) * (32 / TW) - 1) / ((WARPS - 6) * (32 / TW));  // km2 <= 128
+  constexpr int PER_STEP = kFtRemapWarps * (32 / TW);       // targets of a column the remap warps cover per step
+  constexpr int NT = (128 + PER_STEP - 1) / PER_STEP;       // km2 <= 128
+  constexpr int THREADS = 32 * (kFtRemapWarps + kFtSolverWarps + 1);
   CUtensorMap mdl, md, mdu, mb, mx1;
   if (!make_tensor_map_2d<R>(&mdl, dl, ncol, nlev, pitch, TW, nlev, 0) || !make_tensor_map_2d<R>(&md, d, ncol, nlev, pitch, TW, nlev, 0) ||
       !make_tensor_map_2d<R>(&mdu, du, ncol, nlev, pitch, TW, nlev, 0) ||
@@ -849,25 +388,14 @@ static int launch_solve_remap(const R* dl, const R* d, const R* du, const R* Bm,
     ++log2p;
   }
   const int64_t ntiles = (ncol + TW - 1) / TW;
-  // prefetch == 1: one CTA per tile, == 2: persistent with CTA-wide phases (both kept for A/B); default: role-split
-  const int form = MINB != 1 ? 1 : tuning().prefetch == 1 ? 1 : tuning().prefetch == 2 ? 2 : 0;
-  const unsigned grid = (unsigned)(form != 1 ? tmin<int64_t>(ntiles, kNumSms) : ntiles);
+  const unsigned grid = (unsigned)tmin<int64_t>(ntiles, kNumSms);
   int rc;
-#define EKB_FT_LAUNCH(L2_)                                                                                         \
-  if (form == 0) {                                                                                                 \
-    auto k = k_solve_remap_roles<R, L2_, TW, WARPS - 6, 5, RNT>;                                                   \
-    if ((rc = allow_smem(k, smem))) return rc;                                                                     \
-    k<<<grid, 32 * WARPS, smem, stream>>>(mdl, md, mdu, mb, mx1, x2, Y2, X, ncol, nlev, km2, nrhs, pitch, P,        \
-                                          (int)ntiles);                                                            \
-  } else if (form == 2) {                                                                                          \
-    auto k = k_solve_remap_persist<R, L2_, TW, WARPS, NT>;                                                         \
-    if ((rc = allow_smem(k, smem))) return rc;                                                                     \
-    k<<<grid, 32 * WARPS, smem, stream>>>(mdl, md, mdu, mb, mx1, x2, Y2, X, ncol, nlev, km2, nrhs, pitch, P,        \
-                                          (int)ntiles);                                                            \
-  } else {                                                                                                         \
-    auto k = k_solve_remap<R, L2_, TW, WARPS, NT, MINB>;                                                           \
-    if ((rc = allow_smem(k, smem))) return rc;                                                                     \
-    k<<<grid, 32 * WARPS, smem, stream>>>(mdl, md, mdu, mb, mx1, x2, Y2, X, ncol, nlev, km2, nrhs, pitch, P);       \
+#define EKB_FT_LAUNCH(L2_)                                                                                     \
+  {                                                                                                            \
+    auto k = k_solve_remap_roles<R, L2_, TW, kFtRemapWarps, kFtSolverWarps, NT>;                               \
+    if ((rc = allow_smem(k, smem))) return rc;                                                                 \
+    k<<<grid, THREADS, smem, stream>>>(mdl, md, mdu, mb, mx1, x2, Y2, X, ncol, nlev, km2, nrhs, pitch, P,       \
+                                       (int)ntiles);                                                           \
   }
   if (log2p == 6) EKB_FT_LAUNCH(6)
   else if (log2p == 7) EKB_FT_LAUNCH(7)
@@ -877,6 +405,8 @@ static int launch_solve_remap(const R* dl, const R* d, const R* du, const R* Bm,
   return check_cuda(cudaGetLastError());
 }
 
+// Returns EKAT_B200_ERR_UNSUPPORTED when the tile does not fit on chip, the operands do not meet TMA's requirements or
+// the shape is one the two-pass path serves better (a single right-hand side: nothing to amortise the search over).
 template <typename R>
 int solve_remap_tma(const R* dl, const R* d, const R* du, const R* Bm, const R* x1, const R* x2, R* Y2, R* X, int64_t ncol,
                     int nlev, int km2, int nrhs, int64_t pitch, cudaStream_t stream) {
@@ -885,16 +415,21 @@ int solve_remap_tma(const R* dl, const R* d, const R* du, const R* Bm, const R* 
   if (!al(dl) || !al(d) || !al(du) || !al(Bm) || !al(x1) || (pitch * sizeof(R)) % 16) return EKAT_B200_ERR_UNSUPPORTED;
   if (nlev < 2 || nlev > 256 || km2 < 1 || km2 > 128) return EKAT_B200_ERR_UNSUPPORTED;
   if (ncol >= (int64_t)1 << 31 || (int64_t)nrhs * nlev >= (int64_t)1 << 31) return EKAT_B200_ERR_UNSUPPORTED;
+  // few right-hand sides: too little to amortise the search and the factorisation over, the two-pass path is faster
+  // (f64, 345,600 x 128: 1 rhs 0.73 vs 1.04 ms, 3 rhs 1.35 vs 1.49 ms, 4 rhs 1.62 vs 1.55 ms)
+  if (nrhs < (sizeof(R) == 8 ? 4 : 3) && tuning().cols_per_cta == 0) return EKAT_B200_ERR_UNSUPPORTED;
   const int nch = (nlev + kLB - 1) / kLB;
   auto smem_for = [&](int tw) {
     const size_t plane = ((size_t)nlev * tw * sizeof(R) + 127) & ~(size_t)127;
     return (((size_t)(3 + 2 * nrhs + nch) * 8 + (size_t)(nrhs + 1) * 4 + 127) & ~(size_t)127) + (size_t)(4 + nrhs) * plane;
   };
-  const int tw = tuning().cols_per_cta == 8 || tuning().cols_per_cta == 16 ? tuning().cols_per_cta
-                 : 16;
-  if (smem_for(tw) > kMaxSmemPerCta) return EKAT_B200_ERR_UNSUPPORTED;
-  if (tw == 8) return launch_solve_remap<R, 8, 8, 4, 2>(dl, d, du, Bm, x1, x2, Y2, X, ncol, nlev, km2, nrhs, pitch, smem_for(8), stream);
-  return launch_solve_remap<R, 16, 16, 4, 1>(dl, d, du, Bm, x1, x2, Y2, X, ncol, nlev, km2, nrhs, pitch, smem_for(16), stream);
+  // 128-byte rows: 16 columns of f64, 32 of f32 (tuning: cols_per_cta = 16 forces 16 for f32 as well)
+  if constexpr (sizeof(R) == 4) {
+    if (tuning().cols_per_cta != 16 && smem_for(32) <= kMaxSmemPerCta)
+      return launch_solve_remap<R, 32>(dl, d, du, Bm, x1, x2, Y2, X, ncol, nlev, km2, nrhs, pitch, smem_for(32), stream);
+  }
+  if (smem_for(16) > kMaxSmemPerCta) return EKAT_B200_ERR_UNSUPPORTED;
+  return launch_solve_remap<R, 16>(dl, d, du, Bm, x1, x2, Y2, X, ncol, nlev, km2, nrhs, pitch, smem_for(16), stream);
 }
 
 template int solve_remap_tma<double>(const double*, const double*, const double*, const double*, const double*, const double*,

@@ -61,7 +61,8 @@ def test_checksum_and_residual_equal_oracle(cuda, port, dt):
 def test_fused_solve_and_remap(cuda, port, dt):
     """BASELINE config 4 shape (reduced column count): 10-RHS shared-A solve + remap of the 10 solutions."""
     npdt, tdt = DT[dt]
-    for ncol, nlev, km2, nrhs in [(200, 128, 128, 10), (37, 72, 128, 3), (50, 33, 17, 1), (4744, 128, 128, 10), (1000, 72, 72, 4)]:
+    for ncol, nlev, km2, nrhs in [(200, 128, 128, 10), (37, 72, 128, 3), (50, 33, 17, 1), (4744, 128, 128, 10), (1000, 72, 72, 4),
+                                  (5000, 33, 17, 5), (2500, 100, 60, 7), (148 * 32 * 2 + 5, 64, 128, 4)]:
         A, B = port.fill_tridiag(npdt, ncol, nlev, 1, nrhs, col0=4)
         x1, _, x2 = synth.lin_interp_inputs(npdt, ncol, nlev, km2, 1, col0=4)
         Xref = port.tridiag("thomas", A.copy(), B.copy())                       # [ncol,nlev,nrhs]
@@ -76,6 +77,10 @@ def test_fused_solve_and_remap(cuda, port, dt):
         tridiag_lin_interp(dl, d, du, Bd, x1d, x2d, Y2, Xd)
         assert rel_diff(Xref, x_from_lev(Xd.cpu().numpy())) <= tol(npdt)
         assert rel_diff(Yref, Y2.cpu().numpy().transpose(0, 2, 1)) <= 10 * tol(npdt)
+        # the remap half is bit-identical to LinInterp applied to the solutions the kernel itself produced
+        Xg = np.ascontiguousarray(x_from_lev(Xd.cpu().numpy()).transpose(2, 0, 1))
+        Yg, _ = port.lin_interp(x1, x2, Xg, nlev, km2, 1)
+        assert bits_equal(Yg, np.ascontiguousarray(Y2.cpu().numpy().transpose(0, 2, 1)))
         # and it equals the unfused GPU path (thomas, then LinInterp on the transposed solution) to tolerance
         Y2b = torch.zeros_like(Y2)
         tridiag_lin_interp(dl, d, du, Bd, x1d, x2d, Y2b, None)
