@@ -33,9 +33,6 @@
 
 namespace ekb {
 
-// An empty asm the value passes through: the compiler can no longer see where it came from and keeps it in a register.
-__device__ __forceinline__ void pin(double& v) { asm volatile("" : "+d"(v)); }
-__device__ __forceinline__ void pin(float& v) { asm volatile("" : "+f"(v)); }
 
 // One chunk of LB levels of a solver lane's sweeps over planes [level][TW]; pm, pr, pc, px point at the chunk's first
 // level of the lane's column, nrem = levels left from there. FULL: all LB levels exist (constant offsets, no guards).
@@ -416,8 +413,9 @@ int solve_remap_tma(const R* dl, const R* d, const R* du, const R* Bm, const R* 
   if (nlev < 2 || nlev > 256 || km2 < 1 || km2 > 128) return EKAT_B200_ERR_UNSUPPORTED;
   if (ncol >= (int64_t)1 << 31 || (int64_t)nrhs * nlev >= (int64_t)1 << 31) return EKAT_B200_ERR_UNSUPPORTED;
   // few right-hand sides: too little to amortise the search and the factorisation over, the two-pass path is faster
-  // (f64, 345,600 x 128: 1 rhs 0.73 vs 1.04 ms, 3 rhs 1.35 vs 1.49 ms, 4 rhs 1.62 vs 1.55 ms)
-  if (nrhs < (sizeof(R) == 8 ? 4 : 3) && tuning().cols_per_cta == 0) return EKAT_B200_ERR_UNSUPPORTED;
+  // (345,600 x 128, two-pass vs this kernel: f64 3 rhs 1.20 vs 1.49 ms, 4 rhs 1.45 vs 1.55, 5 rhs 1.61 vs 1.56,
+  //  6 rhs 2.15 vs 1.63; f32 1 rhs 0.54 vs 0.50, 2 rhs 0.79 vs 0.57)
+  if (nrhs < (sizeof(R) == 8 ? 5 : 2) && tuning().cols_per_cta == 0) return EKAT_B200_ERR_UNSUPPORTED;
   const int nch = (nlev + kLB - 1) / kLB;
   auto smem_for = [&](int tw) {
     const size_t plane = ((size_t)nlev * tw * sizeof(R) + 127) & ~(size_t)127;

@@ -21,14 +21,16 @@ namespace ekb {
 constexpr int kLmWarps = 8;
 
 // TW = tile width in columns (16 or 32): lane = (target parity, column) for TW = 16. NSY field stages in flight.
-// REG: per-target state in registers across the fields (km2 <= NT * kLmWarps * 32 / TW), else the index map in shared memory.
-template <typename R, int LOG2P, int TW, bool REG>
-__global__ void __launch_bounds__(32 * kLmWarps, REG ? 3 : 4)
+// NTP > 0: per-target state in registers across the fields, NTP targets per thread (km2 <= NTP * kLmWarps * 32 / TW);
+// NTP == 0: the index map in shared memory.
+template <typename R, int LOG2P, int TW, int NTP>
+__global__ void __launch_bounds__(32 * kLmWarps, NTP == 0 ? 4 : NTP <= 8 ? 3 : 2)
 k_lin_interp_lm(const __grid_constant__ CUtensorMap mx1, const __grid_constant__ CUtensorMap my1, const R* __restrict__ x2,
                 R* __restrict__ y2, int64_t ncol, int km1, int km2, int64_t pitch, int nf, int P, int NSY) {
   constexpr unsigned B = sizeof(R), ROW = TW * B;
   constexpr int TPS = 32 / TW;  // targets per warp step
-  constexpr int NT = 8;         // REG: targets per thread
+  constexpr bool REG = NTP > 0;
+  constexpr int NT = REG ? NTP : 1;  // REG: targets per thread
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);  // [0] x1 landed, [1 + s] field stage s landed
   const size_t tile = (((size_t)km1 * ROW + 127) & ~(size_t)127) / B;  // elements per staged tile (TMA wants 128-byte aligned boxes)
@@ -65,44 +67,58 @@ k_lin_interp_lm(const __grid_constant__ CUtensorMap mx1, const __grid_constant__
     // interval x1[k1ph] - x1[k1] and the refined reciprocal of the interval -- the part of the IEEE division that does
     // not depend on the numerator (common.cuh: div_given_rcp is bit-identical to __ddiv_rn). A field then costs two
     // gathers, a subtraction, a product, the quotient's three fused steps and an addition per target.
+    // No branch on j < km2 or on the division's rare operands inside the loops: a thread's NT targets are independent
+    // chains (shared-memory probes, then fp64 latency) and must be free to interleave. Surplus slots redo the last
+    // target and are never stored; div_spec records operands its fast path is not proven for and the field is then
+    // redone with the full-range division (common.cuh).
     unsigned off[NT];
     R dxt[NT], dx[NT], rc[NT];
 #pragma unroll
     for (int t = 0; t < NT; ++t) {
-      const int j = warp * TPS + sub + t * (kLmWarps * TPS);
-      off[t] = 0;
-      dxt[t] = (R)0;
-      dx[t] = (R)1;
-      rc[t] = (R)1;
-      if (j < km2) {
-        const R xt = __ldg(x2 + (size_t)j * pitch + gcol);
-        const unsigned o = bracket_off<R, LOG2P, ROW>(x1a, km1, P, xt);
-        const unsigned oph = o == last_off ? o - ROW : o + ROW;  // k1ph, :119-131
-        const R xa = lds_at(x1a + o, R()), xb = lds_at(x1a + oph, R());
-        off[t] = o;
-        dxt[t] = x_sub(xt, xa);
-        dx[t] = x_sub(xb, xa);
-        rc[t] = rcp_refined(dx[t]);
-      }
+      const int j = tmin(warp * TPS + sub + t * (kLmWarps * TPS), km2 - 1);
+      const R xt = __ldg(x2 + (size_t)j * pitch + gcol);
+      const unsigned o = bracket_off<R, LOG2P, ROW>(x1a, km1, P, xt);
+      const unsigned oph = o == last_off ? o - ROW : o + ROW;  // k1ph, :119-131
+      const R xa = lds_at(x1a + o, R()), xb = lds_at(x1a + oph, R());
+      off[t] = o;
+      dxt[t] = x_sub(xt, xa);
+      dx[t] = x_sub(xb, xa);
+      rc[t] = rcp_refined(dx[t]);
+      pin(dxt[t]);  // left to itself the compiler recomputes these per field instead of keeping them
+      pin(dx[t]);
+      pin(rc[t]);
     }
+    const int j0 = warp * TPS + sub;
+    const size_t tstride = (size_t)(kLmWarps * TPS) * pitch;
+    R* gy = y2 + (size_t)j0 * pitch + col;
     int s = 0;
     unsigned ph = 0;
-    for (int f = 0; f < nf; ++f) {
+    for (int f = 0; f < nf; ++f, gy += (size_t)km2 * pitch) {
       mbar_wait(&bars[1 + s], ph);
       const unsigned y1a = smem_u32(sy + (size_t)s * tile) + (unsigned)lc * B;
-      R* gy = y2 + ((size_t)f * km2) * pitch + col;
+      bool bad = false;
 #pragma unroll
       for (int t = 0; t < NT; ++t) {
-        const int j = warp * TPS + sub + t * (kLmWarps * TPS);
-        if (j < km2) {
+        const unsigned o = off[t];
+        const unsigned oph = o == last_off ? o - ROW : o + ROW;
+        const R ya = lds_at(y1a + o, R()), yb = lds_at(y1a + oph, R());
+        R v = x_sub(yb, ya);                   // :153
+        v = x_mul(v, dxt[t]);                  // :154
+        v = div_spec(v, dx[t], rc[t], bad);    // :155
+        v = x_add(v, ya);                      // :156
+        if (live && j0 + t * (kLmWarps * TPS) < km2) st_stream(gy + t * tstride, v);
+      }
+      if (__builtin_expect(bad, 0)) {
+#pragma unroll
+        for (int t = 0; t < NT; ++t) {
           const unsigned o = off[t];
           const unsigned oph = o == last_off ? o - ROW : o + ROW;
           const R ya = lds_at(y1a + o, R()), yb = lds_at(y1a + oph, R());
-          R v = x_sub(yb, ya);                   // :153
-          v = x_mul(v, dxt[t]);                  // :154
-          v = div_given_rcp(v, dx[t], rc[t]);    // :155
-          v = x_add(v, ya);                      // :156
-          if (live) st_stream(gy + (size_t)j * pitch, v);
+          R v = x_sub(yb, ya);
+          v = x_mul(v, dxt[t]);
+          v = x_div_full(v, dx[t]);
+          v = x_add(v, ya);
+          if (live && j0 + t * (kLmWarps * TPS) < km2) st_stream(gy + t * tstride, v);
         }
       }
       __syncthreads();  // every warp is done with stage s
@@ -162,7 +178,11 @@ int lin_interp_lm(const R* x1, const R* x2, const R* y1, R* y2, int64_t ncol, in
   // tile width and field stages: 16-column tiles (128-byte rows for f64), two field stages -> 52 KB, four CTAs per SM;
   // tuning: cols_per_cta = 16 | 32, prefetch = stages
   const Tuning tu = tuning();
-  const int tw = tu.cols_per_cta == 32 ? 32 : 16;
+  // 128-byte rows: 16 columns of f64, 32 of f32 (f32, 128 -> 64, 10 fields: 93% of the HBM peak against 48% with 16)
+  // -- but 128 targets of 32 columns are 16 per thread, 128 registers and two CTAs per SM, which only pays when there
+  // are fields to spread the search over (f32 128 -> 128: 1 field 35% against 47%, 10 fields 65% against 49%)
+  const int tw = tu.cols_per_cta == 32 || tu.cols_per_cta == 16 ? tu.cols_per_cta
+                 : (sizeof(R) == 4 && (km2 <= 8 * kLmWarps || nfields >= 4)) ? 32 : 16;
   int nsy = tu.prefetch >= 1 && tu.prefetch <= 8 ? tu.prefetch : 2;  // measured: residency (4 CTAs per SM) beats deeper staging
   if (nsy > nfields) nsy = nfields;
   auto smem_for = [&](int st) {
@@ -182,22 +202,24 @@ int lin_interp_lm(const R* x1, const R* x2, const R* y1, R* y2, int64_t ncol, in
     ++log2p;
   }
   const unsigned grid = (unsigned)((ncol + tw - 1) / tw);
-  // per-target state in registers when there are fields to share it between (f64, 10 fields: 71% against 61-64% of the
-  // HBM peak; f32: 50% against 44%); with one field the shared-memory map's higher residency wins.
-  // tuning variant 1 / 2 force the shared-memory map / the register form
-  const bool reg = km2 <= 8 * kLmWarps * (32 / tw) && tu.variant != 1 && (nfields >= 5 || tu.variant == 2);
+  // per-target state in registers whenever a thread's targets fit (km2 <= 8 per thread): f64 128 -> 128, 1 / 2 / 4 / 10
+  // fields: 69 / 76 / 81 / 82% of the HBM peak against 53 / 57 / 63 / 76% for the shared-memory map with its rolled,
+  // branching loop. tuning variant 1 forces the shared-memory map.
+  const int per_step = kLmWarps * (32 / tw);
+  const int ntp = tu.variant == 1 ? 0 : km2 <= 8 * per_step ? 8 : (sizeof(R) == 4 && km2 <= 16 * per_step) ? 16 : 0;
   int rc;
-#define EKB_LM_LAUNCH2(L2_, TW_)                                                                       \
+#define EKB_LM_LAUNCH3(L2_, TW_, NTP_)                                                                 \
   {                                                                                                    \
-    if (reg) {                                                                                         \
-      auto k = k_lin_interp_lm<R, L2_, TW_, true>;                                                     \
-      if ((rc = allow_smem(k, smem))) return rc;                                                       \
-      k<<<grid, 32 * kLmWarps, smem, stream>>>(mx1, my1, x2, y2, ncol, km1, km2, pitch, nfields, P, nsy); \
-    } else {                                                                                           \
-      auto k = k_lin_interp_lm<R, L2_, TW_, false>;                                                    \
-      if ((rc = allow_smem(k, smem))) return rc;                                                       \
-      k<<<grid, 32 * kLmWarps, smem, stream>>>(mx1, my1, x2, y2, ncol, km1, km2, pitch, nfields, P, nsy); \
-    }                                                                                                  \
+    auto k = k_lin_interp_lm<R, L2_, TW_, NTP_>;                                                       \
+    if ((rc = allow_smem(k, smem))) return rc;                                                         \
+    k<<<grid, 32 * kLmWarps, smem, stream>>>(mx1, my1, x2, y2, ncol, km1, km2, pitch, nfields, P, nsy); \
+  }
+#define EKB_LM_LAUNCH2(L2_, TW_)                                 \
+  {                                                              \
+    if (ntp == 8) EKB_LM_LAUNCH3(L2_, TW_, 8)                    \
+    else if (ntp == 16) {                                        \
+      if constexpr (sizeof(R) == 4) EKB_LM_LAUNCH3(L2_, TW_, 16) \
+    } else EKB_LM_LAUNCH3(L2_, TW_, 0)                           \
   }
 #define EKB_LM_LAUNCH(L2_)            \
   if (tw == 32) EKB_LM_LAUNCH2(L2_, 32) \
@@ -207,6 +229,7 @@ int lin_interp_lm(const R* x1, const R* x2, const R* y1, R* y2, int64_t ncol, in
   else EKB_LM_LAUNCH(0)
 #undef EKB_LM_LAUNCH
 #undef EKB_LM_LAUNCH2
+#undef EKB_LM_LAUNCH3
   note_launch(sizeof(R) == 8 ? "lin_interp_lm<f64>" : "lin_interp_lm<f32>");
   return check_cuda(cudaGetLastError());
 }
