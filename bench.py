@@ -380,6 +380,8 @@ def run_extras(torch, dev, peak):
     del dl, d, du, Bm, x1, x2, Y2
     torch.cuda.empty_cache()
     # ReductionUtils::view_reduction and the layout marshalling, config 5 shard size
+    torch.cuda.synchronize()
+    time.sleep(0.5)  # let the board settle after the 10-rhs kernels: the first row here read 15% low right behind them
     from ekat_b200.reduction import view_reduction
     ncol = 3145728
     x = torch.rand((ncol, 128), dtype=torch.float64, device=dev)
