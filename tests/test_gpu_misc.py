@@ -62,7 +62,7 @@ def test_fused_solve_and_remap(cuda, port, dt):
     """BASELINE config 4 shape (reduced column count): 10-RHS shared-A solve + remap of the 10 solutions."""
     npdt, tdt = DT[dt]
     for ncol, nlev, km2, nrhs in [(200, 128, 128, 10), (37, 72, 128, 3), (50, 33, 17, 1), (4744, 128, 128, 10), (1000, 72, 72, 4),
-                                  (5000, 33, 17, 5), (2500, 100, 60, 7), (148 * 32 * 2 + 5, 64, 128, 4)]:
+                                  (5000, 33, 17, 5), (2500, 100, 60, 7), (148 * 32 * 2 + 8, 64, 128, 4)]:
         A, B = port.fill_tridiag(npdt, ncol, nlev, 1, nrhs, col0=4)
         x1, _, x2 = synth.lin_interp_inputs(npdt, ncol, nlev, km2, 1, col0=4)
         Xref = port.tridiag("thomas", A.copy(), B.copy())                       # [ncol,nlev,nrhs]
@@ -85,6 +85,35 @@ def test_fused_solve_and_remap(cuda, port, dt):
         Y2b = torch.zeros_like(Y2)
         tridiag_lin_interp(dl, d, du, Bd, x1d, x2d, Y2b, None)
         assert rel_diff(Y2.cpu().numpy(), Y2b.cpu().numpy()) <= 10 * tol(npdt)  # (may take the one-kernel path: other thomas rounding)
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+def test_fused_repeatable_and_equal_to_two_pass(cuda, dt):
+    """The one-kernel path hands shared-memory planes between warps through mbarriers, several tiles per CTA: any
+    missed hand-over shows as run-to-run differences. Ten runs must be bit-identical, and agree with the two-pass path
+    (other thomas rounding: tolerance) -- at a size where every CTA walks 6+ tiles."""
+    from ekat_b200._lib import lib
+    from ekat_b200.lin_interp import fill as li_fill
+    tdt = DT[dt][1]
+    ncol, nlev, km2, nrhs = 148 * 32 * 6 + 8, 128, 128, 10  # (pitch = ncol must keep rows 16-byte aligned for TMA)
+    dl, d, du, B = T.fill(tdt, ncol, nlev, 1, nrhs, device=cuda)
+    x1, _, x2 = li_fill(tdt, ncol, nlev, km2, 1, device=cuda, lev_major=True)
+    Y, X = torch.zeros((nrhs, km2, ncol), dtype=tdt, device=cuda), torch.zeros_like(B)
+    tridiag_lin_interp(dl[0], d[0], du[0], B, x1, x2, Y, X)
+    assert lib().ekat_b200_last_kernel().decode().startswith("solve_remap_tma")
+    for _ in range(9):
+        Y2, X2 = torch.full_like(Y, float("nan")), torch.full_like(X, float("nan"))
+        tridiag_lin_interp(dl[0], d[0], du[0], B, x1, x2, Y2, X2)
+        assert torch.equal(Y2.view(torch.uint8), Y.view(torch.uint8)) and torch.equal(X2.view(torch.uint8), X.view(torch.uint8))
+    lib().ekat_b200_set_tuning(0, 0, 3)  # two passes: persistent solve out of place, then level-major LinInterp
+    try:
+        Y3 = torch.zeros_like(Y)
+        tridiag_lin_interp(dl[0], d[0], du[0], B, x1, x2, Y3, None)
+        assert not lib().ekat_b200_last_kernel().decode().startswith("solve_remap_tma")
+    finally:
+        lib().ekat_b200_set_tuning(0, 0, 0)
+    scale = float(Y3.abs().max())
+    assert float((Y - Y3).abs().max()) <= 10 * tol(DT[dt][0]) * scale
 
 
 @pytest.mark.parametrize("dt", ["f64", "f32"])
