@@ -138,7 +138,8 @@ __global__ void __launch_bounds__(32 * (NIW + NSW + 1), 1)
 k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
                     const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mb,
                     const __grid_constant__ CUtensorMap mx1, const R* __restrict__ x2, R* __restrict__ Y2,
-                    R* __restrict__ X, int64_t ncol, int nlev, int km2, int nrhs, int64_t pitch, int P, int ntiles) {
+                    R* __restrict__ X, int64_t ncol, int nlev, int km2, int nrhs, int64_t pitch, int P, int ntiles,
+                    int hb) {
   constexpr int WARPS = NIW + NSW + 1, LB = kLB, RN = TmaCfg<R>::RN, TPS = 32 / TW;
   constexpr unsigned B = sizeof(R), ROW = TW * B;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -157,8 +158,9 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
   uint64_t* lbar = bars + 3;
   uint64_t* sbar = lbar + nrhs;
   uint64_t* fbar = sbar + nrhs;
-  int* cnt = reinterpret_cast<int*>(fbar + nch);
-  const size_t bar_bytes = ((size_t)(3 + 2 * nrhs + nch) * 8 + (size_t)(nrhs + 1) * 4 + 127) & ~(size_t)127;
+  uint64_t* bbar = fbar + nch;  // lower half of dl, d, du landed (when they come as two boxes of hb levels)
+  int* cnt = reinterpret_cast<int*>(bbar + 1);
+  const size_t bar_bytes = ((size_t)(4 + 2 * nrhs + nch) * 8 + (size_t)(nrhs + 1) * 4 + 127) & ~(size_t)127;
   const size_t plane = (((size_t)nlev * ROW + 127) & ~(size_t)127) / B;  // elements per plane
   R* PM = reinterpret_cast<R*>(smem_raw + bar_bytes);  // dl -> multipliers
   R* PR = PM + plane;                                  // d  -> reciprocal pivots
@@ -167,21 +169,34 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
   R* PX = PX1 + plane;                                 // [nrhs] right-hand sides -> solutions
   const unsigned plane_bytes = (unsigned)nlev * ROW;
   const int first = blockIdx.x, step = (int)gridDim.x;  // grid <= ntiles
+  // dl, d, du of a tile: one box of nlev levels per plane, or (hb < nlev) two boxes of hb levels with a barrier each,
+  // so that the factor warp -- on the critical path between two tiles -- can start when the upper half is there
+  auto load_A = [&](int tile) {
+    const unsigned half = (unsigned)hb * ROW;
+    mbar_expect_tx(&bars[1], 3u * half);
+    tma_load_2d(PM, &mdl, tile * TW, 0, &bars[1]);
+    tma_load_2d(PR, &md, tile * TW, 0, &bars[1]);
+    tma_load_2d(PC, &mdu, tile * TW, 0, &bars[1]);
+    if (hb < nlev) {
+      mbar_expect_tx(bbar, 3u * half);
+      tma_load_2d(PM + hb * TW, &mdl, tile * TW, hb, bbar);
+      tma_load_2d(PR + hb * TW, &md, tile * TW, hb, bbar);
+      tma_load_2d(PC + hb * TW, &mdu, tile * TW, hb, bbar);
+    }
+  };
   const int nsw = tmin(NSW, (nrhs + TPS - 1) / TPS);     // solver warps that have a right-hand side
 
   if (tid == 0) {
     mbar_init(&bars[0], 1);
     mbar_init(&bars[1], 1);
+    mbar_init(bbar, 1);
     mbar_init(abar, nsw);
     for (int i = 0; i < 2 * nrhs + nch; ++i) mbar_init(&lbar[i], 1);
     for (int r = 0; r <= nrhs; ++r) cnt[r] = 0;
     fence_mbar_init();
     mbar_expect_tx(&bars[0], plane_bytes);
     tma_load_2d(PX1, &mx1, first * TW, 0, &bars[0]);
-    mbar_expect_tx(&bars[1], 3u * plane_bytes);
-    tma_load_2d(PM, &mdl, first * TW, 0, &bars[1]);
-    tma_load_2d(PR, &md, first * TW, 0, &bars[1]);
-    tma_load_2d(PC, &mdu, first * TW, 0, &bars[1]);
+    load_A(first);
     for (int r = 0; r < nrhs; ++r) {
       mbar_expect_tx(&lbar[r], plane_bytes);
       tma_load_2d(PX + (size_t)r * plane, &mb, first * TW, r * nlev, &lbar[r]);
@@ -198,15 +213,13 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
         mbar_wait(abar, par ^ 1u);  // the solvers are done with the previous tile's factors
         if (lane == 0) {
           fence_proxy_async();
-          mbar_expect_tx(&bars[1], 3u * plane_bytes);
-          tma_load_2d(PM, &mdl, tile * TW, 0, &bars[1]);
-          tma_load_2d(PR, &md, tile * TW, 0, &bars[1]);
-          tma_load_2d(PC, &mdu, tile * TW, 0, &bars[1]);
+          load_A(tile);
         }
       }
       mbar_wait(&bars[1], par);
       R q1 = (R)1, q2 = (R)0, cp = (R)0, gp = (R)0;
       for (int k = 0; k < nch; ++k) {
+        if (hb < nlev && k == hb / LB) mbar_wait(bbar, par);  // the first chunk that reaches into the lower half
         const int o = k * LB * TW + lc, nrem = nlev - k * LB;
         if (nrem >= LB) factor_chunk<R, TW, true>(PM + o, PR + o, PC + o, nrem, k == 0, q1, q2, cp, gp);
         else factor_chunk<R, TW, false>(PM + o, PR + o, PC + o, nrem, k == 0, q1, q2, cp, gp);
@@ -374,8 +387,9 @@ static int launch_solve_remap(const R* dl, const R* d, const R* du, const R* Bm,
   constexpr int NT = (128 + PER_STEP - 1) / PER_STEP;       // km2 <= 128
   constexpr int THREADS = 32 * (kFtRemapWarps + kFtSolverWarps + 1);
   CUtensorMap mdl, md, mdu, mb, mx1;
-  if (!make_tensor_map_2d<R>(&mdl, dl, ncol, nlev, pitch, TW, nlev, 0) || !make_tensor_map_2d<R>(&md, d, ncol, nlev, pitch, TW, nlev, 0) ||
-      !make_tensor_map_2d<R>(&mdu, du, ncol, nlev, pitch, TW, nlev, 0) ||
+  const int hb = (nlev % 2 == 0 && nlev >= 32 && tuning().prefetch != 1) ? nlev / 2 : nlev;  // levels per box of dl, d, du
+  if (!make_tensor_map_2d<R>(&mdl, dl, ncol, nlev, pitch, TW, hb, 0) || !make_tensor_map_2d<R>(&md, d, ncol, nlev, pitch, TW, hb, 0) ||
+      !make_tensor_map_2d<R>(&mdu, du, ncol, nlev, pitch, TW, hb, 0) ||
       !make_tensor_map_2d<R>(&mb, Bm, ncol, (int64_t)nrhs * nlev, pitch, TW, nlev, 0) ||
       !make_tensor_map_2d<R>(&mx1, x1, ncol, nlev, pitch, TW, nlev, 0))
     return EKAT_B200_ERR_UNSUPPORTED;
@@ -392,7 +406,7 @@ static int launch_solve_remap(const R* dl, const R* d, const R* du, const R* Bm,
     auto k = k_solve_remap_roles<R, L2_, TW, kFtRemapWarps, kFtSolverWarps, NT>;                               \
     if ((rc = allow_smem(k, smem))) return rc;                                                                 \
     k<<<grid, THREADS, smem, stream>>>(mdl, md, mdu, mb, mx1, x2, Y2, X, ncol, nlev, km2, nrhs, pitch, P,       \
-                                       (int)ntiles);                                                           \
+                                       (int)ntiles, hb);                                                       \
   }
   if (log2p == 6) EKB_FT_LAUNCH(6)
   else if (log2p == 7) EKB_FT_LAUNCH(7)
@@ -419,7 +433,7 @@ int solve_remap_tma(const R* dl, const R* d, const R* du, const R* Bm, const R* 
   const int nch = (nlev + kLB - 1) / kLB;
   auto smem_for = [&](int tw) {
     const size_t plane = ((size_t)nlev * tw * sizeof(R) + 127) & ~(size_t)127;
-    return (((size_t)(3 + 2 * nrhs + nch) * 8 + (size_t)(nrhs + 1) * 4 + 127) & ~(size_t)127) + (size_t)(4 + nrhs) * plane;
+    return (((size_t)(4 + 2 * nrhs + nch) * 8 + (size_t)(nrhs + 1) * 4 + 127) & ~(size_t)127) + (size_t)(4 + nrhs) * plane;
   };
   // 128-byte rows: 16 columns of f64, 32 of f32 (tuning: cols_per_cta = 16 forces 16 for f32 as well)
   if constexpr (sizeof(R) == 4) {
