@@ -62,7 +62,8 @@ def test_fused_solve_and_remap(cuda, port, dt):
     """BASELINE config 4 shape (reduced column count): 10-RHS shared-A solve + remap of the 10 solutions."""
     npdt, tdt = DT[dt]
     for ncol, nlev, km2, nrhs in [(200, 128, 128, 10), (37, 72, 128, 3), (50, 33, 17, 1), (4744, 128, 128, 10), (1000, 72, 72, 4),
-                                  (5000, 33, 17, 5), (2500, 100, 60, 7), (148 * 32 * 2 + 8, 64, 128, 4)]:
+                                  (5000, 33, 17, 5), (2500, 100, 60, 7), (148 * 32 * 2 + 8, 64, 128, 4),
+                                  (64, 5, 9, 6), (96, 2, 3, 5), (1024, 256, 128, 5), (320, 16, 128, 12)]:
         A, B = port.fill_tridiag(npdt, ncol, nlev, 1, nrhs, col0=4)
         x1, _, x2 = synth.lin_interp_inputs(npdt, ncol, nlev, km2, 1, col0=4)
         Xref = port.tridiag("thomas", A.copy(), B.copy())                       # [ncol,nlev,nrhs]
