@@ -35,6 +35,8 @@ for _t in ("f64", "f32"):
     _SIGS[f"ekat_b200_lin_interp_host_{_t}"] = [vp, vp, vp, vp, vp, i64, cint, cint, i64, i64, cint, i64, i64]
 _SIGS["ekat_b200_pipeline_create"] = [ctypes.POINTER(vp), ctypes.c_size_t, cint]
 _SIGS["ekat_b200_pipeline_destroy"] = [vp]
+_SIGS["ekat_b200_pipeline_set_deferred"] = [vp, cint]
+_SIGS["ekat_b200_pipeline_sync"] = [vp]
 _SIGS["ekat_b200_pipeline_stats"] = [vp, ctypes.POINTER(u64), ctypes.POINTER(u64), ctypes.POINTER(u64)]
 _SIGS["ekat_b200_selftest_div_f64"] = [u64, u64, cint, vp, vp]
 _SIGS["ekat_b200_selftest_div_f32"] = [u64, u64, cint, vp, vp]

@@ -3,6 +3,7 @@
 // per-thread error/tuning state and the process-wide launch counter.
 #include <atomic>
 #include <cstring>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -77,6 +78,35 @@ int check_cuda(cudaError_t e) {
   return EKAT_B200_ERR_CUDA;
 }
 Tuning tuning() { return t_tuning; }
+
+// (kernel, device) -> largest dynamic shared memory size already granted by cudaFuncSetAttribute. The attribute
+// belongs to the process, so the table does too (a per-thread table would let one thread lower what another needs).
+struct SmemGrant {
+  const void* kernel;
+  int device;
+  size_t bytes;
+};
+constexpr int kSmemSlots = 128;
+static SmemGrant t_grants[kSmemSlots] = {};
+static std::mutex g_grant_mutex;
+static inline SmemGrant& grant_slot(const void* kernel, int device) {
+  const uint64_t h = (reinterpret_cast<uintptr_t>(kernel) >> 4) * 0x9E3779B97F4A7C15ull + (uint64_t)device;
+  return t_grants[(h >> 32) % kSmemSlots];
+}
+bool smem_attr_needed(const void* kernel, size_t bytes) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return true;
+  std::lock_guard<std::mutex> lock(g_grant_mutex);
+  const SmemGrant& g = grant_slot(kernel, dev);
+  return !(g.kernel == kernel && g.device == dev && g.bytes >= bytes);
+}
+void smem_attr_granted(const void* kernel, size_t bytes) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return;
+  std::lock_guard<std::mutex> lock(g_grant_mutex);
+  SmemGrant& g = grant_slot(kernel, dev);
+  g = {kernel, dev, bytes};
+}
 
 enum { SOLVER_THOMAS = 0, SOLVER_BFB = 1, SOLVER_CR = 2 };
 

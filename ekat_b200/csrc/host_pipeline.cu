@@ -40,6 +40,8 @@ struct ekat_b200_pipeline {
   unsigned char* dev = nullptr;
   cudaStream_t streams[8] = {};
   uint64_t h2d = 0, d2h = 0, launches = 0;
+  int deferred = 0;   // 1: the host entry points return once their chunks are enqueued (ekat_b200_pipeline_sync waits)
+  uint64_t next = 0;  // chunk counter across calls: consecutive calls keep rotating through the slots
 };
 
 using namespace ekb;
@@ -58,6 +60,18 @@ int copy2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t widt
 int64_t chunk_cols(int64_t cap, int64_t ncol, int nslots) {
   const int64_t want = ((ncol + 2 * nslots - 1) / (2 * nslots) + 63) & ~(int64_t)63;
   return tmin<int64_t>(cap, tmax<int64_t>(want, tmin<int64_t>(cap, 1 << 16)));
+}
+
+// Every exit of a host entry point goes through here. On an error the copies already enqueued on the other slot
+// streams still read and write the caller's host buffers, so all streams are drained before the (first) error is
+// returned; on success the streams are drained unless the pipeline is in deferred mode.
+int finish(ekat_b200_pipeline* p, int rc) {
+  if (rc == EKAT_B200_OK && p->deferred) return EKAT_B200_OK;
+  for (int s = 0; s < p->nslots; ++s) {
+    const cudaError_t e = cudaStreamSynchronize(p->streams[s]);
+    if (rc == EKAT_B200_OK) rc = check_cuda(e);
+  }
+  return rc;
 }
 
 template <typename R>
@@ -80,7 +94,7 @@ int tridiag_host(ekat_b200_pipeline* p, int solver, const R* dl, const R* d, con
   int k = 0;
   for (int64_t c0 = 0; c0 < ncol; c0 += cc, ++k) {
     const int64_t nc = tmin<int64_t>(cc, ncol - c0);
-    const int s = k % p->nslots;
+    const int s = (int)((p->next + (uint64_t)k) % (uint64_t)p->nslots);
     cudaStream_t st = p->streams[s];
     R* base = reinterpret_cast<R*>(p->dev + (size_t)s * p->slot_bytes);
     int rc;
@@ -88,33 +102,30 @@ int tridiag_host(ekat_b200_pipeline* p, int solver, const R* dl, const R* d, con
       // device chunk: [plane][lev][cc] with pitch cc
       R *ddl = base, *dd = ddl + rowsA * cc, *ddu = dd + rowsA * cc, *dx = ddu + rowsA * cc;
       const size_t w = (size_t)nc * sizeof(R), dp = (size_t)cc * sizeof(R);
-      if ((rc = copy2d(ddl, dp, dl + c0, a_stride * sizeof(R), w, rowsA, cudaMemcpyHostToDevice, st))) return rc;
-      if ((rc = copy2d(dd, dp, d + c0, a_stride * sizeof(R), w, rowsA, cudaMemcpyHostToDevice, st))) return rc;
-      if ((rc = copy2d(ddu, dp, du + c0, a_stride * sizeof(R), w, rowsA, cudaMemcpyHostToDevice, st))) return rc;
-      if ((rc = copy2d(dx, dp, X + c0, x_stride * sizeof(R), w, rowsX, cudaMemcpyHostToDevice, st))) return rc;
-      if ((rc = solve_chunk(solver, ddl, dd, ddu, dx, nc, nlev, nA, nrhs, cc, cc, layout, st))) return rc;
-      if ((rc = copy2d(X + c0, x_stride * sizeof(R), dx, dp, w, rowsX, cudaMemcpyDeviceToHost, st))) return rc;
+      if ((rc = copy2d(ddl, dp, dl + c0, a_stride * sizeof(R), w, rowsA, cudaMemcpyHostToDevice, st))) return finish(p, rc);
+      if ((rc = copy2d(dd, dp, d + c0, a_stride * sizeof(R), w, rowsA, cudaMemcpyHostToDevice, st))) return finish(p, rc);
+      if ((rc = copy2d(ddu, dp, du + c0, a_stride * sizeof(R), w, rowsA, cudaMemcpyHostToDevice, st))) return finish(p, rc);
+      if ((rc = copy2d(dx, dp, X + c0, x_stride * sizeof(R), w, rowsX, cudaMemcpyHostToDevice, st))) return finish(p, rc);
+      if ((rc = solve_chunk(solver, ddl, dd, ddu, dx, nc, nlev, nA, nrhs, cc, cc, layout, st))) return finish(p, rc);
+      if ((rc = copy2d(X + c0, x_stride * sizeof(R), dx, dp, w, rowsX, cudaMemcpyDeviceToHost, st))) return finish(p, rc);
     } else {
       // device chunk: [col][lev][p], tightly packed
       const size_t ea = (size_t)nlev * nA, ex = (size_t)nlev * nrhs;
       R *ddl = base, *dd = ddl + ea * cc, *ddu = dd + ea * cc, *dx = ddu + ea * cc;
       const size_t wa = ea * sizeof(R), wx = ex * sizeof(R);
-      if ((rc = copy2d(ddl, wa, dl + c0 * a_stride, a_stride * sizeof(R), wa, nc, cudaMemcpyHostToDevice, st))) return rc;
-      if ((rc = copy2d(dd, wa, d + c0 * a_stride, a_stride * sizeof(R), wa, nc, cudaMemcpyHostToDevice, st))) return rc;
-      if ((rc = copy2d(ddu, wa, du + c0 * a_stride, a_stride * sizeof(R), wa, nc, cudaMemcpyHostToDevice, st))) return rc;
-      if ((rc = copy2d(dx, wx, X + c0 * x_stride, x_stride * sizeof(R), wx, nc, cudaMemcpyHostToDevice, st))) return rc;
-      if ((rc = solve_chunk(solver, ddl, dd, ddu, dx, nc, nlev, nA, nrhs, ea, ex, layout, st))) return rc;
-      if ((rc = copy2d(X + c0 * x_stride, x_stride * sizeof(R), dx, wx, wx, nc, cudaMemcpyDeviceToHost, st))) return rc;
+      if ((rc = copy2d(ddl, wa, dl + c0 * a_stride, a_stride * sizeof(R), wa, nc, cudaMemcpyHostToDevice, st))) return finish(p, rc);
+      if ((rc = copy2d(dd, wa, d + c0 * a_stride, a_stride * sizeof(R), wa, nc, cudaMemcpyHostToDevice, st))) return finish(p, rc);
+      if ((rc = copy2d(ddu, wa, du + c0 * a_stride, a_stride * sizeof(R), wa, nc, cudaMemcpyHostToDevice, st))) return finish(p, rc);
+      if ((rc = copy2d(dx, wx, X + c0 * x_stride, x_stride * sizeof(R), wx, nc, cudaMemcpyHostToDevice, st))) return finish(p, rc);
+      if ((rc = solve_chunk(solver, ddl, dd, ddu, dx, nc, nlev, nA, nrhs, ea, ex, layout, st))) return finish(p, rc);
+      if ((rc = copy2d(X + c0 * x_stride, x_stride * sizeof(R), dx, wx, wx, nc, cudaMemcpyDeviceToHost, st))) return finish(p, rc);
     }
     p->h2d += (uint64_t)nc * per_col;
     p->d2h += (uint64_t)nc * rowsX * sizeof(R);
     p->launches += 1;
   }
-  for (int s = 0; s < p->nslots; ++s) {
-    const int rc = check_cuda(cudaStreamSynchronize(p->streams[s]));
-    if (rc) return rc;
-  }
-  return EKAT_B200_OK;
+  p->next += (uint64_t)k;
+  return finish(p, EKAT_B200_OK);
 }
 
 template <typename R>
@@ -131,34 +142,31 @@ int lin_interp_host(ekat_b200_pipeline* p, const R* x1, const R* x2, const R* y1
   int k = 0;
   for (int64_t c0 = 0; c0 < ncol; c0 += cc, ++k) {
     const int64_t nc = tmin<int64_t>(cc, ncol - c0);
-    const int s = k % p->nslots;
+    const int s = (int)((p->next + (uint64_t)k) % (uint64_t)p->nslots);
     cudaStream_t st = p->streams[s];
     R* base = reinterpret_cast<R*>(p->dev + (size_t)s * p->slot_bytes);
     R *dx1 = base, *dx2 = dx1 + cc * pitch1, *dy1 = dx2 + cc * pitch2, *dy2 = dy1 + (size_t)nfields * cc * pitch1;
     int rc;
     const size_t b1 = (size_t)nc * pitch1 * sizeof(R), b2 = (size_t)nc * pitch2 * sizeof(R);
-    if ((rc = check_cuda(cudaMemcpyAsync(dx1, x1 + c0 * pitch1, b1, cudaMemcpyHostToDevice, st)))) return rc;
-    if ((rc = check_cuda(cudaMemcpyAsync(dx2, x2 + c0 * pitch2, b2, cudaMemcpyHostToDevice, st)))) return rc;
+    if ((rc = check_cuda(cudaMemcpyAsync(dx1, x1 + c0 * pitch1, b1, cudaMemcpyHostToDevice, st)))) return finish(p, rc);
+    if ((rc = check_cuda(cudaMemcpyAsync(dx2, x2 + c0 * pitch2, b2, cudaMemcpyHostToDevice, st)))) return finish(p, rc);
     for (int f = 0; f < nfields; ++f)
       if ((rc = check_cuda(cudaMemcpyAsync(dy1 + (size_t)f * cc * pitch1, y1 + (size_t)f * y1_fstride + c0 * pitch1, b1,
                                            cudaMemcpyHostToDevice, st))))
-        return rc;
+        return finish(p, rc);
     rc = lin_interp<R>(0, dx1, dx2, dy1, dy2, nullptr, nullptr, nc, km1, km2, pitch1, pitch2, nfields, cc * pitch1,
                        cc * pitch2, st);
-    if (rc) return rc;
+    if (rc) return finish(p, rc);
     for (int f = 0; f < nfields; ++f)
       if ((rc = check_cuda(cudaMemcpyAsync(y2 + (size_t)f * y2_fstride + c0 * pitch2, dy2 + (size_t)f * cc * pitch2, b2,
                                            cudaMemcpyDeviceToHost, st))))
-        return rc;
+        return finish(p, rc);
     p->h2d += (uint64_t)(b1 * (1 + nfields) + b2);
     p->d2h += (uint64_t)b2 * nfields;
     p->launches += 1;
   }
-  for (int s = 0; s < p->nslots; ++s) {
-    const int rc = check_cuda(cudaStreamSynchronize(p->streams[s]));
-    if (rc) return rc;
-  }
-  return EKAT_B200_OK;
+  p->next += (uint64_t)k;
+  return finish(p, EKAT_B200_OK);
 }
 
 }  // namespace
@@ -188,6 +196,22 @@ int ekat_b200_pipeline_destroy(ekat_b200_pipeline* p) {
   if (p->dev) cudaFree(p->dev);
   delete p;
   return EKAT_B200_OK;
+}
+
+int ekat_b200_pipeline_set_deferred(ekat_b200_pipeline* p, int on) {
+  if (!p) return EKAT_B200_ERR_INVALID;
+  p->deferred = on ? 1 : 0;
+  return EKAT_B200_OK;
+}
+
+int ekat_b200_pipeline_sync(ekat_b200_pipeline* p) {
+  if (!p) return EKAT_B200_ERR_INVALID;
+  int rc = EKAT_B200_OK;
+  for (int s = 0; s < p->nslots; ++s) {
+    const cudaError_t e = cudaStreamSynchronize(p->streams[s]);
+    if (rc == EKAT_B200_OK) rc = check_cuda(e);
+  }
+  return rc;
 }
 
 int ekat_b200_pipeline_stats(ekat_b200_pipeline* p, uint64_t* h2d, uint64_t* d2h, uint64_t* chunks) {

@@ -6,8 +6,11 @@
 
 namespace ekb {
 
-// upper_bound over sorted x1[0..km1): the number of entries <= v, found with the reference's predicate
-// `v >= *it` (ekat_upper_bound.hpp:37-48), so ties and NaNs resolve identically; then the reference's
+// upper_bound over sorted x1[0..km1): the number of entries <= v, found with the predicate `v >= *it` of the
+// reference's EKAT_ENABLE_GPU variant (ekat_upper_bound.hpp:28-50) -- the variant this library replaces. Ties
+// resolve identically in both reference variants; a NaN target fails every `>=` and maps to index 0 here and in
+// the GPU variant, whereas the host variant (std::upper_bound, `!(v < *it)`, :51-53) would map it to km1-1
+// (tests/test_gpu_lin_interp.py::test_nan_targets_follow_the_gpu_upper_bound_variant). Then the reference's
 // "if (idx > 0) --idx" (:179-181). Branch-free: one probe picks the power-of-two window [0,P) or [km1-P,km1)
 // (P = bit_floor(km1)) that must contain the boundary, then log2(P) probes with halving steps and a last one --
 // each a shared-memory load, a compare and a predicated add. LOG2P > 0: unrolled for that window; 0: loop.

@@ -207,23 +207,29 @@ __global__ void k_tridiag_lm_shared(R* __restrict__ dl, R* __restrict__ d, R* __
   int64_t c0;
   int nlive;
   own_columns<CPT>(((int64_t)blockIdx.x * Tc + t) * CPT, ncol, c0, nlive);
-  const int j0 = blockIdx.y * G;
-  const int jn = min(G, nrhs - j0);
-
-  if (role_a) {
-    if (tid < Tc)
-      lm_factorize<R, EXACT, CLOBBER, PF, CPT>(dl + c0, d + c0, du + c0, a_stride, nlev, f0, f1, f2, Tc, t,
-                                               blockIdx.y == 0 ? nlive : 0);
-  } else if (ty < Ty) {
-    for (int jj = ty; jj < jn; jj += Ty)
-      lm_issue_rhs<R, CPT>(X + (size_t)(j0 + jj) * nlev * x_stride + c0, x_stride, nlev, sx + (size_t)jj * plane, Tc, t);
-    cp_async_wait<0>();
-  }
-  __syncthreads();
-  if (!role_a && ty < Ty) {
-    for (int jj = ty; jj < jn; jj += Ty)
-      lm_solve<R, EXACT, CPT, false>(f0, f1, f2, sx + (size_t)jj * plane, Tc, t, nlev,
-                                     X + (size_t)(j0 + jj) * nlev * x_stride + c0, x_stride, nlive);
+  // CLOBBER writes the factorisation back into dl/d, so the matrix may be read from HBM only once per column: the
+  // CTA then walks every right-hand-side group itself (gridDim.y == 1) instead of one group per blockIdx.y -- with
+  // one CTA per group the later groups would factorise the multipliers/pivots the first one had already stored.
+  const int ngroups = (nrhs + G - 1) / G;
+  const int g_begin = CLOBBER ? 0 : (int)blockIdx.y, g_end = CLOBBER ? ngroups : (int)blockIdx.y + 1;
+  for (int g = g_begin; g < g_end; ++g) {
+    const int j0 = g * G;
+    const int jn = min(G, nrhs - j0);
+    if (role_a) {
+      if (tid < Tc && g == g_begin)
+        lm_factorize<R, EXACT, CLOBBER, PF, CPT>(dl + c0, d + c0, du + c0, a_stride, nlev, f0, f1, f2, Tc, t, nlive);
+    } else if (ty < Ty) {
+      for (int jj = ty; jj < jn; jj += Ty)
+        lm_issue_rhs<R, CPT>(X + (size_t)(j0 + jj) * nlev * x_stride + c0, x_stride, nlev, sx + (size_t)jj * plane, Tc, t);
+      cp_async_wait<0>();
+    }
+    __syncthreads();
+    if (!role_a && ty < Ty) {
+      for (int jj = ty; jj < jn; jj += Ty)
+        lm_solve<R, EXACT, CPT, false>(f0, f1, f2, sx + (size_t)jj * plane, Tc, t, nlev,
+                                       X + (size_t)(j0 + jj) * nlev * x_stride + c0, x_stride, nlive);
+    }
+    if (g + 1 < g_end) __syncthreads();  // the rhs planes are reused by the next group
   }
 }
 
@@ -276,7 +282,7 @@ static int launch_shared(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int n
   int rc = allow_smem(k, smem);
   if (rc) return rc;
   const int64_t tc = (int64_t)Tc * CPT;
-  dim3 grid((unsigned)((ncol + tc - 1) / tc), (unsigned)((nrhs + G - 1) / G));
+  dim3 grid((unsigned)((ncol + tc - 1) / tc), CLOBBER ? 1u : (unsigned)((nrhs + G - 1) / G));
   k<<<grid, 32 + Tc * Ty, smem, stream>>>(dl, d, du, X, ncol, nlev, nrhs, G, Tc, a_stride, x_stride);
   note_launch(name);
   return check_cuda(cudaGetLastError());

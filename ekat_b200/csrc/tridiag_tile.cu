@@ -26,7 +26,8 @@ enum TileAlgo { ALGO_THOMAS = 0, ALGO_BFB = 1, ALGO_CR = 2 };
 struct TileArgs {
   void *dl, *d, *du, *X;
   int64_t ncol, a_stride, x_stride;
-  int nlev, nA, nrhs, C, Cp, lev_major, clobber;
+  int nlev, nA, nrhs, C, Cp, lev_major;
+  int clobber;  // planes written back under EKAT_B200_CLOBBER_DIAGS: bit 0 dl, bit 1 d, bit 2 du (0: none)
 };
 
 template <typename R>
@@ -90,9 +91,9 @@ __device__ __forceinline__ void tile_drain(const TileArgs& a, const R* sdl, cons
       for (int e = tid; e < na * nc; e += nthr) {
         const int r = e / nc, c = e - r * nc;
         const size_t g = (size_t)r * a.a_stride + c0 + c;
-        st_stream(gdl + g, sdl[(size_t)r * Cp + c]);
-        st_stream(gd + g, sd[(size_t)r * Cp + c]);
-        st_stream(gdu + g, sdu[(size_t)r * Cp + c]);
+        if (a.clobber & 1) st_stream(gdl + g, sdl[(size_t)r * Cp + c]);
+        if (a.clobber & 2) st_stream(gd + g, sd[(size_t)r * Cp + c]);
+        if (a.clobber & 4) st_stream(gdu + g, sdu[(size_t)r * Cp + c]);
       }
   } else {
     const int na = nlev * nA, nx = nlev * nrhs;
@@ -107,9 +108,9 @@ __device__ __forceinline__ void tile_drain(const TileArgs& a, const R* sdl, cons
         const int i = k / nA, p = k - i * nA;
         const size_t g = (size_t)(c0 + c) * a.a_stride + k;
         const size_t s = ((size_t)p * nlev + i) * Cp + c;
-        st_stream(gdl + g, sdl[s]);
-        st_stream(gd + g, sd[s]);
-        st_stream(gdu + g, sdu[s]);
+        if (a.clobber & 1) st_stream(gdl + g, sdl[s]);
+        if (a.clobber & 2) st_stream(gd + g, sd[s]);
+        if (a.clobber & 4) st_stream(gdu + g, sdu[s]);
       }
   }
 }
@@ -321,7 +322,14 @@ int tridiag_tile(int algo, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int
   a.ncol = ncol; a.a_stride = a_stride; a.x_stride = x_stride;
   a.nlev = nlev; a.nA = nA; a.nrhs = nrhs; a.C = C; a.Cp = Cp;
   a.lev_major = layout == EKAT_B200_LAYOUT_LEV_MAJOR;
-  a.clobber = (flags & EKAT_B200_CLOBBER_DIAGS) != 0;
+  // What the reference's in-place solvers leave behind (ekat_tridiag.hpp): serial thomas -- pivots in d (:216-227);
+  // bfb / team thomas -- multipliers in dl, pivots in d (:292-303, :177-193); cr -- all three reduced (:415-417).
+  // du is never modified by thomas / bfb. The reciprocal-form sweep below keeps 1/pivot, m*r and du*r in the staged
+  // planes, so a thomas call that must write the pivots back runs the bfb sweep instead (same operations, each
+  // rounded once: within the thomas tolerance by construction, and d comes out bit-identical to the reference's).
+  const bool clobber = (flags & EKAT_B200_CLOBBER_DIAGS) != 0;
+  a.clobber = !clobber ? 0 : (algo == ALGO_CR ? 7 : (algo == ALGO_BFB ? 3 : 2));
+  if (clobber && algo == ALGO_THOMAS) algo = ALGO_BFB;
 
   const int64_t ntiles = (ncol + C - 1) / C;
   int per_sm = (int)(kMaxSmemPerCta / (smem + 1024));

@@ -30,6 +30,13 @@ class Pipeline:
         except Exception:
             pass
 
+    def set_deferred(self, on=True):
+        """Deferred mode: tridiag()/lin_interp() return once their chunks are enqueued; sync() waits for all of them."""
+        check("ekat_b200_pipeline_set_deferred", lib().ekat_b200_pipeline_set_deferred(self._h, 1 if on else 0))
+
+    def sync(self):
+        check("ekat_b200_pipeline_sync", lib().ekat_b200_pipeline_sync(self._h))
+
     def stats(self):
         a, b, c = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64()
         check("ekat_b200_pipeline_stats", lib().ekat_b200_pipeline_stats(self._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)))
@@ -47,10 +54,24 @@ class Pipeline:
         return X
 
     def lin_interp(self, x1, x2, y1, y2, km1, km2):
+        """Host tensors x1,[y1]: [ncol][pitch1] ([nfields][ncol][pitch1]); x2,[y2]: [ncol][pitch2]; y2 is overwritten."""
+        if x1.dim() != 2 or x2.dim() != 2 or x1.shape[0] != x2.shape[0]:
+            raise ValueError("x1 [ncol][pitch1] and x2 [ncol][pitch2] expected")
         ncol, pitch1 = x1.shape
         pitch2 = x2.shape[1]
         y1f = y1 if y1.dim() == 3 else y1.unsqueeze(0)
         y2f = y2 if y2.dim() == 3 else y2.unsqueeze(0)
+        if y1f.shape[0] != y2f.shape[0] or tuple(y1f.shape[1:]) != (ncol, pitch1) or tuple(y2f.shape[1:]) != (ncol, pitch2):
+            raise ValueError("y1 must be [nfields][ncol][pitch1] and y2 [nfields][ncol][pitch2]")
+        if not (2 <= km1 <= pitch1 and 0 <= km2 <= pitch2):
+            raise ValueError("km1/km2 outside the row pitch")
+        for t in (x1, x2, y1f, y2f):
+            if t.is_cuda:
+                raise ValueError("Pipeline.lin_interp takes host tensors")
+            if t.dtype != x1.dtype or t.dtype not in _SFX:
+                raise ValueError("x1, x2, y1, y2 must share one dtype (float32 or float64)")
+            if not t.is_contiguous():
+                raise ValueError("Pipeline.lin_interp takes contiguous tensors")
         fn = f"ekat_b200_lin_interp_host_{_SFX[x1.dtype]}"
         check(fn, getattr(lib(), fn)(self._h, x1.data_ptr(), x2.data_ptr(), y1f.data_ptr(), y2f.data_ptr(), ncol, km1, km2,
                                      pitch1, pitch2, y1f.shape[0], ncol * pitch1, ncol * pitch2))

@@ -103,10 +103,14 @@ class LinInterp:
         return y2
 
 
-def fill(dtype, ncol, km1, km2, pack_size=1, col0=0, seed=20260411, device="cuda", lev_major=False):
+def fill(dtype, ncol, km1, km2, pack_size=1, col0=0, seed=20260411, device="cuda", lev_major=False, out=None):
     """Device-side synthetic LinInterp inputs: returns x1, y1, x2.
-    Reference layout [ncol, npack*N] (pack padding lanes zero), or level-major [km, ncol] if lev_major."""
-    if lev_major:
+    Reference layout [ncol, npack*N] (pack padding lanes zero), or level-major [km, ncol] if lev_major.
+    out = (x1, y1, x2) from an earlier call of the same shape family: refill the first ncol columns in place."""
+    if out is not None:
+        x1, y1, x2 = out
+        p1, p2 = (x1.shape[1], x2.shape[1])
+    elif lev_major:
         x1 = torch.zeros((km1, ncol), dtype=dtype, device=device)
         y1 = torch.zeros((km1, ncol), dtype=dtype, device=device)
         x2 = torch.zeros((km2, ncol), dtype=dtype, device=device)

@@ -142,10 +142,14 @@ def lev_to_col(src, ncol=None):
     return dst
 
 
-def fill(dtype, ncol, nlev, nA, nrhs, layout=LEV_MAJOR, col0=0, seed_mod=32768, device="cuda", pitch=None):
+def fill(dtype, ncol, nlev, nA, nrhs, layout=LEV_MAJOR, col0=0, seed_mod=32768, device="cuda", pitch=None, out=None):
     """Device-side reference fills (tests/algorithm/tridiag_tests.hpp:11-40), seed = (col0+c) % seed_mod.
-    Returns (dl, d, du, X) in the requested layout."""
-    if layout == LEV_MAJOR:
+    Returns (dl, d, du, X) in the requested layout. out = (dl, d, du, X) from an earlier call with the same layout
+    and a pitch >= ncol: refill those buffers in place (a resident chunk buffer streamed over a larger batch)."""
+    if out is not None:
+        dl, d, du, X = out
+        _, _, _, _, a_stride, x_stride = _geometry(dl, d, du, X, layout, ncol)
+    elif layout == LEV_MAJOR:
         pitch = ncol if pitch is None else pitch
         A = torch.empty((3, nA, nlev, pitch), dtype=dtype, device=device)
         X = torch.empty((nrhs, nlev, pitch), dtype=dtype, device=device)

@@ -15,7 +15,11 @@
  * Conventions
  *  - every data pointer is a DEVICE pointer unless the name says "host";
  *  - asynchronous on `stream` (a cudaStream_t; 0 = legacy default stream);
- *  - no global state, no allocation, no synchronisation inside;
+ *  - no allocation and no synchronisation inside; no global DATA state -- the
+ *    only process-wide state is bookkeeping: the launch counter, per-thread
+ *    last-error / last-kernel strings, per-thread tuning overrides, a
+ *    per-thread cache of encoded TMA descriptors keyed by (pointer, shape,
+ *    pitch, box), and a debug trace buffer used by one instrumented variant;
  *  - returns EKAT_B200_OK or a negative ekat_b200_status; never throws, never
  *    aborts (the reference's debug `assert`s and EKAT_KERNEL_REQUIRE aborts,
  *    src/algorithm/ekat_tridiag.hpp:184-185,328-330 and
@@ -262,12 +266,23 @@ int ekat_b200_fill_lin_interp_f32(float* x1, float* y1, float* x2, int64_t ncol,
  * 260-303). Columns are cut into chunks that flow through a multi-stream
  * upload -> solve -> download pipeline; device staging belongs to an explicit
  * pipeline object (device_bytes split over nslots <= 8 slots, one stream each).
- * Synchronous: results are on the host when the call returns. dl/d/du are not
- * modified. solver: 0 thomas, 1 bfb, 2 cr.
+ * Synchronous by default: results are on the host when the call returns.
+ * dl/d/du are not modified. solver: 0 thomas, 1 bfb, 2 cr.
+ * Deferred mode (ekat_b200_pipeline_set_deferred(p, 1)): a host entry point
+ * returns as soon as its chunks are enqueued, so that consecutive calls on one
+ * pipeline overlap -- the upload of the next call's first chunks runs under the
+ * download of the previous call's last ones (the slots keep rotating across
+ * calls; stream order protects their reuse). The host buffers of every
+ * enqueued call belong to the pipeline until ekat_b200_pipeline_sync returns.
+ * On any error an entry point first drains all of the pipeline's streams (no
+ * copy still touches the caller's buffers after an error return) and reports
+ * the first error.
  * ---------------------------------------------------------------------- */
 typedef struct ekat_b200_pipeline ekat_b200_pipeline;
 int ekat_b200_pipeline_create(ekat_b200_pipeline** out, size_t device_bytes, int nslots);
 int ekat_b200_pipeline_destroy(ekat_b200_pipeline* p);
+int ekat_b200_pipeline_set_deferred(ekat_b200_pipeline* p, int on);
+int ekat_b200_pipeline_sync(ekat_b200_pipeline* p); /* waits for every enqueued chunk; first CUDA error, if any */
 /* totals since creation: bytes uploaded, bytes downloaded, chunks processed */
 int ekat_b200_pipeline_stats(ekat_b200_pipeline* p, uint64_t* h2d_bytes, uint64_t* d2h_bytes, uint64_t* chunks);
 int ekat_b200_tridiag_host_f64(ekat_b200_pipeline* p, int solver, const double* dl, const double* d,

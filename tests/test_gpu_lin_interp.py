@@ -177,3 +177,27 @@ def test_level_major_parity_bitwise(cuda, port, dt):
         if km1 == km2:  # in place
             lin_interp_lm(tx1, tx2, ty1, ty1, ncol=ncol)
             assert bits_equal(np.ascontiguousarray(ty1.cpu().numpy()[:, :, :ncol].transpose(0, 2, 1)), want)
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+def test_nan_targets_follow_the_gpu_upper_bound_variant(cuda, port, dt):
+    """ekat::upper_bound has two variants (src/kokkos/ekat_upper_bound.hpp:28-53): the EKAT_ENABLE_GPU build's own
+    loop with the predicate `value >= *it`, and std::upper_bound (`!(value < *it)`) on host builds. They agree on
+    every ordered input and differ only for a NaN target: every `>=` is false, so the GPU variant returns index 0
+    where std::upper_bound returns km1 - 1. This library replaces the GPU build, so it matches the GPU variant
+    (and so does the oracle port, which restates that loop): the index map of a NaN target is 0 and its value NaN.
+    The other targets of the column are unaffected."""
+    npdt, tdt = DT[dt]
+    for km1, km2, N in [(72, 128, 1), (128, 128, 16), (33, 70, 4)]:
+        x1, y1, x2 = synth.lin_interp_inputs(npdt, 40, km1, km2, N, col0=3)
+        x2[5, 7] = np.nan
+        x2[9, 0] = np.nan
+        x2[9, km2 - 1] = np.nan
+        want, wim = port.lin_interp(x1, x2, y1, km1, km2, N)
+        for mode in ("fused", "setup_apply"):
+            got, gim = gpu_interp(cuda, tdt, x1, x2, y1, km1, km2, N, mode)
+            assert np.array_equal(gim, wim)
+            assert gim[5, 7] == 0 and gim[9, 0] == 0 and gim[9, km2 - 1] == 0
+            assert np.isnan(got[5, 7]) and np.isnan(got[9, 0]) and np.isnan(got[9, km2 - 1])
+            ok = ~np.isnan(want[:, :km2])
+            assert bits_equal(got[:, :km2][ok], want[:, :km2][ok])

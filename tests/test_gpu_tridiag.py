@@ -115,8 +115,46 @@ def test_clobber_diags_matches_reference_side_effect(cuda, port, dt, layout):
         port.tridiag("thomas", Aref2, Xref2)
         got2, Aout2 = run_gpu("thomas", A, B, layout, cuda, clobber=True)
         assert rel_diff(Xref2, got2) <= tol(npdt)
-        if layout == ekat_b200.LEV_MAJOR:
-            assert rel_diff(Aref2[:, 1], Aout2[:, 1]) <= tol(npdt)
+        assert rel_diff(Aref2[:, 1], Aout2[:, 1]) <= tol(npdt), "thomas: pivots in d (:221), both layouts"
+        assert bits_equal(Aout2[:, 2], A[:, 2]), "thomas never modifies du"
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+@pytest.mark.parametrize("solver", ["bfb", "thomas"])
+def test_clobber_diags_many_rhs_groups(cuda, port, dt, solver):
+    """CLOBBER_DIAGS with more right-hand sides than one CTA holds (several rhs groups per column tile, e.g. the
+    reference perf driver's default 128 rows x 43 rhs, tridiag_tests_performance.cpp:33-37): the matrix must be
+    factorised from the ORIGINAL dl/d exactly once per column whatever the number of groups -- X and the
+    clobbered dl/d bit-identical to the reference (bfb) / within tolerance (thomas), many columns."""
+    npdt, _ = DT[dt]
+    for nrhs, nrow, ncol in [(12, 128, 1500), (43, 128, 700), (24, 72, 1111)]:
+        A, B = port.fill_tridiag(npdt, ncol, nrow, 1, nrhs, col0=5)
+        Aref, Xref = A.copy(), B.copy()
+        port.tridiag("bfb", Aref, Xref)
+        got, Aout = run_gpu(solver, A, B, ekat_b200.LEV_MAJOR, cuda, clobber=True)
+        if solver == "bfb":
+            assert bits_equal(got, Xref), (nrhs, nrow, rel_diff(Xref, got))
+            assert bits_equal(Aout[:, 0, 1:], Aref[:, 0, 1:]), "dl multipliers"
+            assert bits_equal(Aout[:, 1], Aref[:, 1]), "d pivots"
+        else:
+            assert rel_diff(Xref, got) <= tol(npdt), (nrhs, nrow, rel_diff(Xref, got))
+            assert rel_diff(Aref[:, 1], Aout[:, 1]) <= tol(npdt)
+        assert bits_equal(Aout[:, 2], A[:, 2]), "du untouched"
+
+
+def test_against_the_unchanged_reference_headers(cuda, ref):
+    """The GPU path against oracle/_ref itself (the reference's own headers compiled where they lie), not only
+    against the plain-C port: bfb and cr bit for bit, thomas to tolerance, single / shared / per-rhs matrices."""
+    if ref is None:
+        pytest.skip("oracle/_ref not built (needs /root/reference at build time)")
+    for npdt in (np.float64, np.float32):
+        for nrow, nrhs, nA in [(72, 1, 1), (128, 10, 1), (128, 10, 10), (129, 3, 1)]:
+            A, B = ref.fill_tridiag(npdt, 333, nrow, nA, nrhs, col0=7)
+            for solver in ("bfb", "cr", "thomas"):
+                want = ref.tridiag(solver, A.copy(), B.copy())
+                for layout in (ekat_b200.LEV_MAJOR, ekat_b200.COL_MAJOR):
+                    got, _ = run_gpu(solver, A, B, layout, cuda, pad=(-333) % 4 if layout == ekat_b200.LEV_MAJOR else 0)
+                    check(solver, got, want, npdt, ("_ref", solver, layout, nrow, nrhs, nA))
 
 
 def test_tuning_variants_agree(cuda, port):

@@ -1,6 +1,7 @@
 """Run a few launches of selected kernels at a fixed shape (for ncu captures):
     python tools/prof_case.py [case ...]   cases: thomas bfb cr li shared fused col  (default: thomas bfb li)
-Each case launches its kernel 3 times at BASELINE config 3 size (345,600 columns x 128 levels, f64)."""
+Each case launches its kernel 3 times at BASELINE config 3 size (345,600 columns x 128 levels, f64) unless
+PROF_NCOL / PROF_NLEV / PROF_DT say otherwise (config 1: PROF_NCOL=21600 PROF_NLEV=72)."""
 import os
 import sys
 
@@ -13,7 +14,7 @@ from ekat_b200 import tridiag as T  # noqa: E402
 from ekat_b200.lin_interp import LinInterp, fill as li_fill, tridiag_lin_interp  # noqa: E402
 
 dev = torch.device("cuda:0")
-NCOL, NLEV = int(os.environ.get("PROF_NCOL", 345600)), 128
+NCOL, NLEV = int(os.environ.get("PROF_NCOL", 345600)), int(os.environ.get("PROF_NLEV", 128))
 dt = torch.float32 if os.environ.get("PROF_DT") == "f32" else torch.float64
 cases = sys.argv[1:] or ["thomas", "bfb", "li"]
 REPS = 3
@@ -51,6 +52,12 @@ for c in cases:
         for _ in range(REPS):
             X.copy_(B)
             getattr(T, c.split("_")[1])(dl, d, du, X, layout=ekat_b200.COL_MAJOR)
+    elif c == "li72":
+        x1, y1, x2 = li_fill(dt, NCOL, 72, 128, 16, device=dev)
+        li = LinInterp(NCOL, 72, 128, dt, 16, device=dev)
+        y2 = torch.zeros((NCOL, 128), dtype=dt, device=dev)
+        for _ in range(REPS):
+            li.run(x1, x2, y1, y2)
     elif c == "li":
         for km1 in (72, 128):
             x1, y1, x2 = li_fill(dt, NCOL, km1, 128, 1, device=dev)
