@@ -126,17 +126,17 @@ static int tridiag_entry(int solver, R* dl, R* d, R* du, R* X, int64_t ncol, int
   }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (solver == SOLVER_CR) {
-    if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && nA == 1 && nrhs == 1 && !flags && tuning().variant == 0) {
+    if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && nA == 1 && nrhs == 1 && !flags && tuning().variant == kVarAuto) {
       const int rc = tridiag_cr_tma<R>(dl, d, du, X, ncol, nlev, a_stride, x_stride, st);  // many columns (tridiag_cr_tma.cu)
       if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
     }
     return tridiag_tile<R>(2, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, layout, flags, st);
   }
-  if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && tuning().variant != 2)
+  if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && tuning().variant != kVarForceTile)
     return tridiag_levmajor<R>(solver == SOLVER_BFB, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, flags, st);
-  if (layout == EKAT_B200_LAYOUT_COL_MAJOR && nA == 1 && nrhs == 1 && !flags && (tuning().variant == 0 || (tuning().variant >= 4 && tuning().variant <= 6) || tuning().variant == 10 || tuning().variant == 11)) {
+  if (layout == EKAT_B200_LAYOUT_COL_MAJOR && nA == 1 && nrhs == 1 && !flags && var_allows_warp_tile(tuning().variant)) {
     // reference layout, one right-hand side: the TMA kernel reads the columns where they lie (tridiag_tma.cu)
-    if (solver == SOLVER_THOMAS && tuning().variant == 0) {  // f64: factor and solve chains on different warps
+    if (solver == SOLVER_THOMAS && tuning().variant == kVarAuto) {  // f64: factor and solve chains on different warps
       const int rc = tridiag_tma_shared_cm<R>(false, dl, d, du, X, ncol, nlev, a_stride, x_stride, st);
       if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
     }

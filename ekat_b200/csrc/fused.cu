@@ -149,8 +149,8 @@ int tridiag_lin_interp(const R* dl, const R* d, const R* du, const R* B, const R
                        int64_t ncol, int nlev, int km2, int nrhs, int64_t pitch, cudaStream_t stream) {
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
   // One kernel, every plane of a 16-column tile on chip (fused_tma.cu), whenever the tile fits: nothing but the inputs
-  // and the remapped fields crosses HBM. Tuning variant 3 skips it (A/B against the two-pass path below).
-  if (tuning().variant == 0) {
+  // and the remapped fields crosses HBM. Tuning variant kVarScalarCopies skips it (A/B against the two-pass path below).
+  if (tuning().variant == kVarAuto) {
     const int rc = solve_remap_tma<R>(dl, d, du, B, x1, x2, Y2, X, ncol, nlev, km2, nrhs, pitch, stream);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }
@@ -159,7 +159,7 @@ int tridiag_lin_interp(const R* dl, const R* d, const R* du, const R* B, const R
   // caller does not ask for them (X == nullptr) they are staged in Y2 itself, which has their shape when
   // km2 == nlev, and interpolated in place tile by tile. The one-kernel version below keeps them on chip but
   // holds only 16 columns per SM and runs at a fifth of this speed (profiles/).
-  if ((tuning().variant == 0 || tuning().variant == 3) && km2 > 0 && (X != nullptr || km2 == nlev)) {
+  if ((tuning().variant == kVarAuto || tuning().variant == kVarScalarCopies) && km2 > 0 && (X != nullptr || km2 == nlev)) {
     R* sol = X ? X : Y2;
     int rc = tridiag_tma_shared_oop<R>(false, const_cast<R*>(dl), const_cast<R*>(d), const_cast<R*>(du), B, sol, ncol, nlev,
                                        nrhs, pitch, pitch, stream);

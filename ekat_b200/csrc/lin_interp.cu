@@ -358,7 +358,7 @@ int lin_interp(int mode, const R* x1, const R* x2, const R* y1, R* y2, int* indx
   auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
   const bool sizes_ok = ((size_t)CB * pitch1 * sizeof(R)) % 16 == 0 && ((size_t)CB * pitch2 * sizeof(R)) % 16 == 0 &&
                         ((size_t)y1_fstride * sizeof(R)) % 16 == 0;
-  const bool use_tma = tu.variant != 1 && sizes_ok && aligned16(x1) && aligned16(x2) && (nf == 0 || aligned16(y1));
+  const bool use_tma = tu.variant != kVarNoTmaStaging && sizes_ok && aligned16(x1) && aligned16(x2) && (nf == 0 || aligned16(y1));
 
   LiArgs a;
   a.x1 = x1; a.x2 = x2; a.y1 = y1; a.y2 = y2; a.indx = indx; a.indx_in = indx_in;
@@ -383,7 +383,7 @@ int lin_interp(int mode, const R* x1, const R* x2, const R* y1, R* y2, int* indx
   // bind before shared memory does, and a CTA that only starts when another has finished all its tiles would run alone.
   // (B200, 1.57 M columns, one-at-a-time vs batched, % of the HBM peak: f64 72->128 79 vs 82, 128->128 94-98 vs 79-92,
   //  128->72 73 vs 71; f32 128->128 60 vs 67, 72->128 53 vs 52, 128->72 58 vs 49)
-  const bool batched = tu.variant == 22 || (tu.variant != 21 && (km1 < km2 || (sizeof(R) == 4 && km1 == km2)));
+  const bool batched = tu.variant == kVarLiBatched || (tu.variant != kVarLiUnbatched && (km1 < km2 || (sizeof(R) == 4 && km1 == km2)));
 #define EKB_LI_LAUNCH_B(MODE_, L2_, U_)                                                                      \
   {                                                                                                          \
     auto k = k_lin_interp_batch<R, MODE_, L2_, U_>;                                                          \

@@ -206,7 +206,7 @@ int lin_interp_lm(const R* x1, const R* x2, const R* y1, R* y2, int64_t ncol, in
   // fields: 69 / 76 / 81 / 82% of the HBM peak against 53 / 57 / 63 / 76% for the shared-memory map with its rolled,
   // branching loop. tuning variant 1 forces the shared-memory map.
   const int per_step = kLmWarps * (32 / tw);
-  const int ntp = tu.variant == 1 ? 0 : km2 <= 8 * per_step ? 8 : (sizeof(R) == 4 && km2 <= 16 * per_step) ? 16 : 0;
+  const int ntp = tu.variant == kVarNoTmaStaging ? 0 : km2 <= 8 * per_step ? 8 : (sizeof(R) == 4 && km2 <= 16 * per_step) ? 16 : 0;
   int rc;
 #define EKB_LM_LAUNCH3(L2_, TW_, NTP_)                                                                 \
   {                                                                                                    \

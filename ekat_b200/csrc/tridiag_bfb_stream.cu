@@ -395,7 +395,7 @@ int tridiag_bfb_stream(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nma
     if (tiles(c) == tiles(2)) ns = c;
   if (tu.cols_per_cta >= 2 && tu.cols_per_cta <= 6 && smem_for(tu.cols_per_cta) <= kMaxSmemPerCta) ns = tu.cols_per_cta;
   const int pd = tu.prefetch > 0 ? tu.prefetch : 4;
-  const bool pp = tu.variant != 6;  // variant 6: one sweeping warp (A/B measurements)
+  const bool pp = tu.variant != kVarStreamOneWarp;  // one sweeping warp (A/B measurements)
   const bool f64 = sizeof(R) == 8;
   const char* name = CM ? (f64 ? "tridiag_bfb_stream_cm<f64>" : "tridiag_bfb_stream_cm<f32>")
                         : (f64 ? "tridiag_bfb_stream<f64>" : "tridiag_bfb_stream<f32>");

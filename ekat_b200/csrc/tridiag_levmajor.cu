@@ -40,6 +40,11 @@ template <typename R>
 int tridiag_tma_shared(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nrhs, int64_t a_stride,
                        int64_t x_stride, cudaStream_t stream);
 
+// One warp per tile, whole tile on chip, for short columns / small batches (tridiag_small.cu).
+template <typename R>
+int tridiag_small(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride, bool force,
+                  cudaStream_t stream);
+
 // ---------------------------------------------------------------------------------------
 // One matrix per rhs (nA == nrhs, incl. nrhs == 1): thread <-> (column group, blockIdx.y = matrix).
 // Planes ([nlev][T] vectors):  EXACT: P0 = d -> d', P1 = x -> x', P2 = du;  ring R0 = dl
@@ -337,17 +342,23 @@ int tridiag_levmajor(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nle
   // for the one-warp kernel); bfb with a single right-hand side is bound by its division chain on either kernel and
   // keeps the one-warp kernel, which holds three tiles per SM instead of two (measured: 54% against 47%); so does f32
   // thomas (72% against 63%: half the bytes per level for the same number of barrier hand-offs).
-  const bool split_ok = nA == 1 && !clobber && (variant == 0 || variant == 7 || variant == 8 || variant == 9);
-  if (split_ok && (nrhs > 1 || (!exact && sizeof(R) == 8) || variant == 7 || variant == 9)) {
+  // Latency-bound batches of short columns (BASELINE config 1): the whole tile on chip, eliminated from both ends
+  // (tridiag_small.cu decides by shape whether it applies; kVarSmall forces it for tests and A/B measurements).
+  if (!exact && nA == nrhs && !clobber && (variant == kVarAuto || variant == kVarSmall)) {
+    const int rc = tridiag_small<R>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, variant == kVarSmall, stream);
+    if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+  }
+  const bool split_ok = nA == 1 && !clobber && var_allows_shared(variant);
+  if (split_ok && (nrhs > 1 || (!exact && sizeof(R) == 8) || var_forces_shared(variant))) {
     const int rc = tridiag_tma_shared<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }
-  if (nA == nrhs && !clobber && (variant == 0 || variant == 4 || variant == 5 || variant == 6 || variant == 10 || variant == 11 || variant == 12)) {
+  if (nA == nrhs && !clobber && var_allows_warp_tile(variant)) {
     const int rc = tridiag_tma<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }
   constexpr int VEC = 16 / sizeof(R);
-  const bool vec = tuning().variant != 3 && vec_ok<R>(dl, d, du, X, a_stride, x_stride);
+  const bool vec = tuning().variant != kVarScalarCopies && vec_ok<R>(dl, d, du, X, a_stride, x_stride);
   if (vec) {
     return exact ? run_levmajor<R, true, VEC>(dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, clobber, stream)
                  : run_levmajor<R, false, VEC>(dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, clobber, stream);

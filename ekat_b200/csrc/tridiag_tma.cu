@@ -837,11 +837,11 @@ static int run_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev,
   // bfb from 96 levels up: input-only copy ring, two sweeping warps (tridiag_bfb_stream.cu). Shorter columns leave room
   // for five or more tiles of the one-sweeping-warp kernel below, which then wins (measured at 72 levels: 79% against
   // 71%; at 96: 74% against 76%; at 128: 66% against 75-82%); so it does for column-major f32 (12-level chunks).
-  if (exact && (tu.variant == 0 || tu.variant == 6) && (nlev >= 96 || tu.variant == 6) && !(CM && sizeof(R) == 4)) {
+  if (exact && (tu.variant == kVarAuto || tu.variant == kVarStreamOneWarp) && (nlev >= 96 || tu.variant == kVarStreamOneWarp) && !(CM && sizeof(R) == 4)) {
     const int rc = tridiag_bfb_stream<R, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, stream);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }
-  if (exact && tu.variant != 4) {
+  if (exact && tu.variant != kVarWarpTileBfb) {
     // bfb: pivots on chip, x' through L2 (k_tridiag_bfb_spill): as many tiles per SM as a 3- or 4-stage ring allows
     const size_t al = CM ? 1024 : 128;
     auto smem_for = [&](int stages) {
@@ -859,11 +859,11 @@ static int run_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev,
       const int pd = tu.prefetch > 0 ? tu.prefetch : 3;
       const char* name = CM ? (f64 ? "tridiag_bfb_spill_cm<f64>" : "tridiag_bfb_spill_cm<f32>")
                             : (f64 ? "tridiag_bfb_spill<f64>" : "tridiag_bfb_spill<f32>");
-      // variant 5: the single-warp form (the sweeping warp issues its own copies), variant 11: two sweeping warps + io
+      // kVarSpillOneWarp: the single-warp form (the sweeping warp issues its own copies), kVarSpillTwoWarps: two sweeping warps + io
       // warp; kept for A/B measurements. Default: one sweeping warp + io warp.
 #define EKB_SPILL(NS_, IO_) launch_spill<R, NS_, CM, IO_>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem_for(NS_), stream, name)
-      if (tu.variant == 5) return ns == 4 ? EKB_SPILL(4, 0) : ns == 3 ? EKB_SPILL(3, 0) : EKB_SPILL(2, 0);
-      if (tu.variant == 11) return ns == 4 ? EKB_SPILL(4, 2) : ns == 3 ? EKB_SPILL(3, 2) : EKB_SPILL(2, 2);
+      if (tu.variant == kVarSpillOneWarp) return ns == 4 ? EKB_SPILL(4, 0) : ns == 3 ? EKB_SPILL(3, 0) : EKB_SPILL(2, 0);
+      if (tu.variant == kVarSpillTwoWarps) return ns == 4 ? EKB_SPILL(4, 2) : ns == 3 ? EKB_SPILL(3, 2) : EKB_SPILL(2, 2);
       return ns == 4 ? EKB_SPILL(4, 1) : ns == 3 ? EKB_SPILL(3, 1) : EKB_SPILL(2, 1);
 #undef EKB_SPILL
     }
@@ -886,7 +886,7 @@ static int run_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev,
   if (exact)
     return ns == 2 ? launch_tma<R, true, 2, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name)
                    : launch_tma<R, true, 4, CM>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name);
-  if (tu.variant == 12)  // io-warp form: measured slower here (f32 69% against 72%; f64 with one matrix per rhs 76% against
+  if (tu.variant == kVarWarpTileIo)  // io-warp form: measured slower here (f32 69% against 72%; f64 with one matrix per rhs 76% against
                          // 78%) -- unlike bfb, whose long chain leaves the sweeping warp no slack; kept for A/B measurements
     return ns == 2 ? launch_tma<R, false, 2, CM, true>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name)
                    : launch_tma<R, false, 4, CM, true>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name);

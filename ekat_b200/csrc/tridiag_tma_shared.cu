@@ -65,7 +65,7 @@ __device__ __forceinline__ void bfb_factor_chunk(const Vec<R, CPT> (&a)[LB], con
   }
 }
 
-// Phase trace for tuning (variant 7 of ekat_b200_set_tuning selects the instrumented instantiation): per traced CTA
+// Phase trace for tuning (variant kVarTrace = 7 of ekat_b200_set_tuning selects the instrumented instantiation): per traced CTA
 // (blockIdx 0 and gridDim/2) and work item < kTraceItems, 16 counters in clock64 cycles -- see trace_put call sites.
 constexpr int kTraceItems = 64, kTraceWords = 16;
 __device__ long long g_trace[2 * kTraceItems * kTraceWords];
@@ -567,9 +567,11 @@ k_tridiag_tma_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
 }
 
 // ------------------------------------------------------------------------------------------- host side
+static inline int shared_threads(int rh, int io) { return 32 * (rh + 3 + (io ? rh : 0)); }
+
 template <typename R, bool EXACT, bool DBG, bool CM>
 static int launch_shared_tma(R* dl, R* d, R* du, R* X, const R* Xin, int64_t ncol, int nlev, int nrhs, int64_t a_stride, int64_t x_stride,
-                             int rh, int ns, size_t smem, cudaStream_t stream, const char* name) {
+                             int rh, int ns, int io, int per_sm, size_t smem, cudaStream_t stream, const char* name) {
   constexpr int CPT = TmaCfg<R>::CPT, RN = EXACT ? 1 : TmaCfg<R>::RN, W = 32 * CPT;
   CUtensorMap mdl, md, mdu, mx, mxin;
   if (CM) {  // [ncol][stride] rows whose first nlev entries are the column; 64-byte rows, swizzled (f64 only)
@@ -589,14 +591,33 @@ static int launch_shared_tma(R* dl, R* d, R* du, R* X, const R* Xin, int64_t nco
   const int ngroups = nrhs / rh;
   const int64_t ntiles = (ncol + W - 1) / W, nwork = ntiles * ngroups;
   if (nwork >= (int64_t)1 << 30) return EKAT_B200_ERR_UNSUPPORTED;
-  const int per_sm = (int)((kMaxSmemPerCta + 1024) / (smem + 1024));
   const int64_t grid = tmin<int64_t>(nwork, (int64_t)kNumSms * tmax(1, per_sm));
-  // one io warp per solver warp (TMA issue off the solver's critical path) while the block stays within 512 threads
-  const int io = (2 * rh + 3) * 32 <= 512 && tuning().variant != 8 ? 1 : 0;
-  k<<<(unsigned)grid, 32 * (rh + 3 + (io ? rh : 0)), smem, stream>>>(mdl, md, mdu, mx, mxin, X, ncol, nlev, x_stride, rh, ngroups,
-                                                                    (int)nwork, ns, io);
+  k<<<(unsigned)grid, shared_threads(rh, io), smem, stream>>>(mdl, md, mdu, mx, mxin, X, ncol, nlev, x_stride, rh, ngroups,
+                                                            (int)nwork, ns, io);
   note_launch(name);
   return check_cuda(cudaGetLastError());
+}
+
+// Resident CTAs per SM of an instantiation at a block size and dynamic shared-memory size (registers and threads
+// bind as well as shared memory). The occupancy query is a driver call, so its answers are remembered per thread.
+template <typename R, bool EXACT, bool CM>
+static int shared_ctas_per_sm(int threads, size_t smem) {
+  struct Memo {
+    int threads;
+    size_t smem;
+    int n;
+  };
+  static thread_local Memo memo[16] = {};
+  static thread_local int used = 0;
+  for (int i = 0; i < used; ++i)
+    if (memo[i].threads == threads && memo[i].smem == smem) return memo[i].n;
+  constexpr int CPT = TmaCfg<R>::CPT, RN = EXACT ? 1 : TmaCfg<R>::RN;
+  auto k = k_tridiag_tma_shared<R, EXACT, CPT, RN, false, CM>;
+  int n = 0;
+  if (allow_smem(k, smem) != EKAT_B200_OK) return 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, threads, smem) != cudaSuccess || n < 1) n = 1;
+  if (used < 16) memo[used++] = {threads, smem, n};
+  return n;
 }
 
 // Returns EKAT_B200_ERR_UNSUPPORTED when the operands do not meet TMA's requirements or a tile does not fit on
@@ -634,16 +655,44 @@ static int run_shared(bool exact, R* dl, R* d, R* du, R* X, const R* Xin, int64_
     }
   if (!rh) return EKAT_B200_ERR_UNSUPPORTED;
   if (tu.prefetch >= 2 && tu.prefetch <= ns) ns = tu.prefetch;  // tuning override: ring stages
-  const size_t smem = smem_for(rh, ns);
+  // one io warp per solver warp (TMA issue off the solver's critical path) while the block stays within 512 threads
+  int io = (2 * rh + 3) * 32 <= 512 && tu.variant != kVarNoIoWarps ? 1 : 0;
+  size_t smem = smem_for(rh, ns);
+  auto ctas = [&](int cio, size_t sm) {
+    return exact ? shared_ctas_per_sm<R, true, CM>(shared_threads(rh, cio), sm) : shared_ctas_per_sm<R, false, CM>(shared_threads(rh, cio), sm);
+  };
+  int per_sm = ctas(io, smem);
+  // Small batches (BASELINE config 1: 21,600 columns x 72 levels = 675 tiles for 148 SMs) are latency-bound: what a
+  // launch costs is the number of WAVES of tiles, each a full forward + backward dependent chain, not bytes. There
+  // the deep ring and the io warps are traded for residency: fewer ring stages (less shared memory) and no io warps
+  // (fewer threads, so registers admit another CTA) until every tile is resident at once, if that is possible.
+  const int64_t nwork = ((ncol + W - 1) / W) * (nrhs / rh);
+  auto waves = [&](int n) { return (nwork + (int64_t)kNumSms * n - 1) / ((int64_t)kNumSms * n); };
+  if (tu.prefetch < 2 && tu.variant == kVarAuto && nwork <= (int64_t)kNumSms * 16 && waves(per_sm) > 1) {
+    int best_ns = ns, best_io = io, best_n = per_sm;
+    for (int cio = io; cio >= 0; --cio)
+      for (int cns = ns; cns >= 2; --cns) {
+        const int n = ctas(cio, smem_for(rh, cns));
+        if (waves(n) < waves(best_n)) {
+          best_ns = cns;
+          best_io = cio;
+          best_n = n;
+        }
+      }
+    ns = best_ns;
+    io = best_io;
+    per_sm = best_n;
+    smem = smem_for(rh, ns);
+  }
   const bool f64 = sizeof(R) == 8;
   const char* name = CM ? (exact ? "tridiag_tma_shared_cm<f64,bfb>" : "tridiag_tma_shared_cm<f64,thomas>")
                         : exact ? (f64 ? "tridiag_tma_shared<f64,bfb>" : "tridiag_tma_shared<f32,bfb>")
                                 : (f64 ? "tridiag_tma_shared<f64,thomas>" : "tridiag_tma_shared<f32,thomas>");
-  if (tu.variant == 7 && !CM)  // instrumented instantiation (phase trace)
-    return exact ? launch_shared_tma<R, true, true, false>(dl, d, du, X, Xin, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name)
-                 : launch_shared_tma<R, false, true, false>(dl, d, du, X, Xin, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name);
-  return exact ? launch_shared_tma<R, true, false, CM>(dl, d, du, X, Xin, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name)
-               : launch_shared_tma<R, false, false, CM>(dl, d, du, X, Xin, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, smem, stream, name);
+  if (tu.variant == kVarTrace && !CM)  // instrumented instantiation (phase trace)
+    return exact ? launch_shared_tma<R, true, true, false>(dl, d, du, X, Xin, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, io, per_sm, smem, stream, name)
+                 : launch_shared_tma<R, false, true, false>(dl, d, du, X, Xin, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, io, per_sm, smem, stream, name);
+  return exact ? launch_shared_tma<R, true, false, CM>(dl, d, du, X, Xin, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, io, per_sm, smem, stream, name)
+               : launch_shared_tma<R, false, false, CM>(dl, d, du, X, Xin, ncol, nlev, nrhs, a_stride, x_stride, rh, ns, io, per_sm, smem, stream, name);
 }
 
 // level-major operands: dl,d,du [nlev][a_stride], X [nrhs][nlev][x_stride]

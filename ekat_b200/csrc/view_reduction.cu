@@ -257,7 +257,7 @@ int view_reduction(const R* in, R* out, int64_t ncol, int begin, int end, int64_
     const size_t tsmem = 16 + (size_t)2 * 32 * TP * sizeof(R);
     const bool ok = (reinterpret_cast<uintptr_t>(in) & 15) == 0 && pitch % E == 0 && tn % E == 0 && tn > 0 &&
                     tsmem <= kMaxSmemPerCta && (packn == 0 || packn == 1 || packn == 2 || packn == 4 || packn == 8 || packn == 16) &&
-                    tuning().variant == 0;
+                    tuning().variant == kVarAuto;
     if (ok) {
       const int per_sm = (int)tmax<size_t>(1, tmin<size_t>(16, (kMaxSmemPerCta + 1024) / (tsmem + 1024)));
       const unsigned grid = (unsigned)tmin<int64_t>(ntiles, (int64_t)148 * per_sm);

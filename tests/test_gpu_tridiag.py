@@ -301,3 +301,37 @@ def test_cr_many_columns_bit_exact(cuda, port, dt):
         assert lib().ekat_b200_last_kernel().decode().startswith("tridiag_cr_tma"), lib().ekat_b200_last_kernel()
         assert bits_equal(got, want), (dt, nrow, ncol, rel_diff(want, got))
         assert bits_equal(Aout, A)
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+def test_small_batch_kernel_two_sided_elimination(cuda, port, dt):
+    """tridiag_small.cu (whole tile on chip, eliminated from both ends, divisions deferred to the substitution):
+    forced through the tuning variant at every reference level count (1..129: no bottom half, partial top chunks,
+    odd splits), ragged tiles, several matrices per launch, and at BASELINE config 1's own shape where it is the
+    default -- against the oracle to the thomas tolerance, plus the reference's residual acceptance test."""
+    from ekat_b200._lib import lib
+    npdt, _ = DT[dt]
+    try:
+        lib().ekat_b200_set_tuning(0, 0, 13)
+        for nrow in NROWS + [7, 9, 17, 24, 25, 48, 71, 72, 73, 96, 200]:
+            for nrhs, nA, ncol in [(1, 1, 37), (3, 3, 70), (1, 1, 64)]:
+                A, B = port.fill_tridiag(npdt, ncol, nrow, nA, nrhs, col0=13)
+                want = port.tridiag("thomas", A.copy(), B.copy())
+                got, Aout = run_gpu("thomas", A, B, ekat_b200.LEV_MAJOR, cuda, pad=(-ncol) % 4)
+                assert lib().ekat_b200_last_kernel().decode().startswith("tridiag_small"), lib().ekat_b200_last_kernel()
+                assert rel_diff(want, got) <= tol(npdt), (dt, nrow, nrhs, rel_diff(want, got))
+                assert bits_equal(Aout, A)
+                assert port.residual(A, B, got) <= 50 * eps(npdt)
+    finally:
+        lib().ekat_b200_set_tuning(0, 0, 0)
+    A, B = port.fill_tridiag(npdt, 21600, 72, 1, 1, col0=0)  # config 1: the default route
+    want = port.tridiag("thomas", A.copy(), B.copy())
+    got, _ = run_gpu("thomas", A, B, ekat_b200.LEV_MAJOR, cuda)
+    assert lib().ekat_b200_last_kernel().decode().startswith("tridiag_small"), lib().ekat_b200_last_kernel()
+    assert rel_diff(want, got) <= tol(npdt)
+    # dl(0) and du(n-1) are never used (ekat_tridiag.hpp:24-27): NaNs there must not reach the solution
+    A2 = A.copy()
+    A2[:, 0, 0, :] = np.nan
+    A2[:, 2, -1, :] = np.nan
+    got2, _ = run_gpu("thomas", A2, B, ekat_b200.LEV_MAJOR, cuda)
+    assert bits_equal(got2, got)
