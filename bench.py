@@ -759,13 +759,70 @@ def run_extras(torch, dev, peak):
     torch.cuda.empty_cache()
     for fn in EXTRA_ROWS:  # rows registered by later additions (3-D marshalling, shift ops, fused difference + solve)
         try:
-            fn(torch, dev, peak, timed, wall, row)
+            fn(torch, dev, peak, timed, wall, row, replay)
         except Exception as e:  # a missing optional row must not cost the bench line
             out.append({"case": getattr(fn, "__name__", "extra"), "error": f"{type(e).__name__}: {e}"[:200]})
     return out
 
 
-EXTRA_ROWS = []
+def rows_round2(torch, dev, peak, timed, wall, row, replay):
+    """SURVEY.md section 8f-3 / 8f-1 rows added in round 2: the fused difference -> diagonals -> solve step beside its
+    two-pass form, the shift / index_and_shift column ops and the rank-3 marshalling."""
+    from ekat_b200 import tridiag as T
+    from ekat_b200.reduction import shift, index_and_shift
+    # ---- fused difference + fill + solve. Algorithmic traffic: z, kd, X in, X out = 4 words per column-level; the
+    # two-pass form moves 10 (diffusion_matrix reads 2 + writes 3, thomas reads 4 + writes 1).
+    for ncol, nlev, small in ((21600, 72, True), (345600, 72, False), (345600, 128, False)):
+        z = torch.cumsum(torch.rand((nlev, ncol), dtype=torch.float64, device=dev) * 300 + 20, 0)
+        kd = torch.rand((nlev, ncol), dtype=torch.float64, device=dev) * 3000
+        B = torch.rand((nlev, ncol), dtype=torch.float64, device=dev)
+        X = B.clone()
+        A = torch.empty((3, 1, nlev, ncol), dtype=torch.float64, device=dev)
+        L = T.lib()
+        zp, kp, xp, s0 = z.data_ptr(), kd.data_ptr(), X.data_ptr(), torch.cuda.current_stream().cuda_stream
+
+        def fused():
+            T.diffusion_solve(z, kd, X)
+
+        def two_pass():
+            L.ekat_b200_diffusion_matrix_f64(zp, kp, A[0].data_ptr(), A[1].data_ptr(), A[2].data_ptr(), ncol, nlev, ncol,
+                                             torch.cuda.current_stream().cuda_stream)
+            T.thomas(A[0], A[1], A[2], X[None])
+
+        alg = 4 * nlev * 8 * ncol
+        for fn, nm, words in ((fused, "fused (one kernel, diagonals never in HBM)", 4), (two_pass, "two passes (diffusion_matrix + thomas)", 10)):
+            if small:
+                ms = replay(fn)
+                kw = {"timing": "graph replay of 50 back-to-back launches"}
+            else:
+                ms = timed(fn, restore=lambda: X.copy_(B))
+                kw = {}
+            row(f"8f-3 difference -> (dl,d,du) -> solve, {ncol:,} x {nlev} f64, {nm}", alg, ncol * nlev, ms,
+                hbm_words_per_column_level=words, frac_of_own_traffic=words * nlev * 8 * ncol / ms / 1e6 / peak, **kw)
+        del z, kd, B, X, A
+        torch.cuda.empty_cache()
+    # ---- shift / index_and_shift, reference layout, config 5 shard
+    ncol = 3145728
+    x = torch.rand((ncol, 128), dtype=torch.float64, device=dev)
+    o = torch.empty_like(x)
+    ms = timed(lambda: shift(x, 1, 0.0, out=o))
+    row(f"8f-3 shift_right, {ncol:,} x 128 f64, reference layout (read + write)", 2 * 128 * 8 * ncol, ncol * 128, ms)
+    idx = torch.randint(0, 127, (ncol, 128), dtype=torch.int32, device=dev)
+    o2 = torch.empty_like(x)
+    ms = timed(lambda: index_and_shift(x, idx, 1, out=o, out_shift=o2))
+    row(f"8f-3 index_and_shift<1>, {ncol:,} x 128 f64 (read a + idx, write 2)", (3 * 8 + 4) * 128 * ncol, ncol * 128, ms)
+    del idx, o, o2, x
+    torch.cuda.empty_cache()
+    # ---- rank-3 marshalling: the reference's X[col][lev][rhs] -> rhs planes [rhs][lev][col]
+    ncol, nrhs = 786432, 10
+    xc = torch.rand((ncol, 128, nrhs), dtype=torch.float64, device=dev)
+    of = torch.empty((nrhs, 128, ncol), dtype=torch.float64, device=dev)
+    ms = timed(lambda: T.transpose3(xc, True, out=of))
+    row(f"8f-1 marshalling X[col][lev][rhs] -> [rhs][lev][col], {ncol:,} x 128 x {nrhs} f64 (read + write)", 2 * 128 * nrhs * 8 * ncol,
+        ncol * 128, ms)
+
+
+EXTRA_ROWS = [rows_round2]
 
 
 def run_e2e(torch, dev, comm, ncol, dl, d, du, B, x1, y1, x2, steps, world):

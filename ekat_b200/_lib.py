@@ -26,6 +26,12 @@ for _t in ("f64", "f32"):
     _SIGS[f"ekat_b200_col_to_lev_{_t}"] = [vp, vp, i64, cint, i64, i64, vp]
     _SIGS[f"ekat_b200_lev_to_col_{_t}"] = [vp, vp, i64, cint, i64, i64, vp]
     _SIGS[f"ekat_b200_adj_diff_{_t}"] = [vp, vp, i64, cint, i64, i64, cint, cint, vp]
+    _SIGS[f"ekat_b200_diffusion_solve_{_t}"] = [vp, vp, vp, i64, cint, i64, vp]
+    _SIGS[f"ekat_b200_diffusion_matrix_{_t}"] = [vp, vp, vp, vp, vp, i64, cint, i64, vp]
+    _SIGS[f"ekat_b200_shift_{_t}"] = [vp, vp, i64, cint, i64, i64, cint, cint, ctypes.c_double if _t == "f64" else ctypes.c_float, vp]
+    _SIGS[f"ekat_b200_index_and_shift_{_t}"] = [vp, vp, vp, vp, i64, cint, cint, i64, i64, i64, cint, cint, vp]
+    _SIGS[f"ekat_b200_transpose3_{_t}"] = [vp, vp, i64, cint, cint, i64, i64, cint, vp]
+    _SIGS[f"ekat_b200_repack_{_t}"] = [vp, vp, i64, cint, i64, i64, cint, vp]
     _SIGS[f"ekat_b200_view_reduction_{_t}"] = [vp, vp, i64, cint, cint, i64, cint, cint, vp]
     _SIGS[f"ekat_b200_checksum_{_t}"] = [vp, i64, i64, i64, vp, vp]
     _SIGS[f"ekat_b200_tridiag_residual_{_t}"] = [vp, vp, vp, vp, vp, i64, cint, cint, cint, i64, vp, vp]

@@ -48,6 +48,20 @@ template <typename R>
 int adj_diff(const R* in, R* out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out, int col_major, int forward,
              cudaStream_t st);
 template <typename R>
+int diffusion_solve(const R* z, const R* kd, R* X, int64_t ncol, int nlev, int64_t pitch, cudaStream_t stream);
+template <typename R>
+int diffusion_matrix(const R* z, const R* kd, R* dl, R* d, R* du, int64_t ncol, int nlev, int64_t pitch, cudaStream_t stream);
+template <typename R>
+int shift(const R* in, R* out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out, int col_major, int s, R fill,
+          cudaStream_t st);
+template <typename R>
+int index_and_shift(const R* a, const int* idx, R* out, R* out_shift, int64_t ncol, int n, int m, int64_t pitch_a,
+                    int64_t pitch_idx, int64_t pitch_out, int col_major, int s, cudaStream_t st);
+template <typename R>
+int transpose3(const R* src, R* dst, int64_t ni, int nk, int nj, int64_t c_stride, int64_t f_pitch, int c2f, cudaStream_t st);
+template <typename R>
+int repack(const R* src, R* dst, int64_t nrows, int n, int64_t src_stride, int64_t dst_pitch, int zero_pad, cudaStream_t st);
+template <typename R>
 int view_reduction(const R* in, R* out, int64_t ncol, int begin, int end, int64_t pitch, int col_major, int packn,
                    cudaStream_t st);
 template <typename R>
@@ -255,6 +269,54 @@ DEF_LI_LM(float, f32)
     if (ncol && n && (!in || !out || in == out)) return EKAT_B200_ERR_INVALID;                                 \
     return adj_diff<T>(in, out, ncol, n, pitch_in, pitch_out, layout == EKAT_B200_LAYOUT_COL_MAJOR, forward,   \
                        ST(s));                                                                                 \
+  }                                                                                                            \
+  int ekat_b200_diffusion_solve_##sfx(const T* z, const T* kd, T* X, int64_t ncol, int nlev, int64_t pitch,    \
+                                      ekat_b200_stream_t s) {                                                  \
+    if (ncol < 0 || nlev < 1 || pitch < ncol) return EKAT_B200_ERR_INVALID;                                    \
+    if (ncol == 0) return EKAT_B200_OK;                                                                        \
+    if (!z || !kd || !X) return EKAT_B200_ERR_INVALID;                                                         \
+    return diffusion_solve<T>(z, kd, X, ncol, nlev, pitch, ST(s));                                             \
+  }                                                                                                            \
+  int ekat_b200_diffusion_matrix_##sfx(const T* z, const T* kd, T* dl, T* d, T* du, int64_t ncol, int nlev,    \
+                                       int64_t pitch, ekat_b200_stream_t s) {                                  \
+    if (ncol < 0 || nlev < 1 || pitch < ncol) return EKAT_B200_ERR_INVALID;                                    \
+    if (ncol && (!z || !kd || !dl || !d || !du)) return EKAT_B200_ERR_INVALID;                                 \
+    return diffusion_matrix<T>(z, kd, dl, d, du, ncol, nlev, pitch, ST(s));                                    \
+  }                                                                                                            \
+  int ekat_b200_shift_##sfx(const T* in, T* out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out,     \
+                            ekat_b200_layout layout, int shift_by, T fill, ekat_b200_stream_t s) {             \
+    if (ncol < 0 || n < 0) return EKAT_B200_ERR_INVALID;                                                       \
+    if (layout != EKAT_B200_LAYOUT_COL_MAJOR && layout != EKAT_B200_LAYOUT_LEV_MAJOR) return EKAT_B200_ERR_INVALID; \
+    const int64_t need = layout == EKAT_B200_LAYOUT_COL_MAJOR ? (int64_t)n : ncol;                             \
+    if (pitch_in < need || pitch_out < need) return EKAT_B200_ERR_INVALID;                                     \
+    if (ncol && n && (!in || !out || in == out)) return EKAT_B200_ERR_INVALID;                                 \
+    return shift<T>(in, out, ncol, n, pitch_in, pitch_out, layout == EKAT_B200_LAYOUT_COL_MAJOR, shift_by,     \
+                    fill, ST(s));                                                                              \
+  }                                                                                                            \
+  int ekat_b200_index_and_shift_##sfx(const T* a, const int* idx, T* out, T* out_shift, int64_t ncol, int n,   \
+                                      int m, int64_t pitch_a, int64_t pitch_idx, int64_t pitch_out,            \
+                                      ekat_b200_layout layout, int shift_by, ekat_b200_stream_t s) {          \
+    if (ncol < 0 || n < 0 || m < 0) return EKAT_B200_ERR_INVALID;                                              \
+    if (layout != EKAT_B200_LAYOUT_COL_MAJOR && layout != EKAT_B200_LAYOUT_LEV_MAJOR) return EKAT_B200_ERR_INVALID; \
+    const bool cm = layout == EKAT_B200_LAYOUT_COL_MAJOR;                                                      \
+    if (pitch_a < (cm ? (int64_t)n : ncol) || pitch_idx < (cm ? (int64_t)m : ncol) ||                          \
+        pitch_out < (cm ? (int64_t)m : ncol))                                                                  \
+      return EKAT_B200_ERR_INVALID;                                                                            \
+    if (ncol && m && (!a || !idx || !out || !out_shift)) return EKAT_B200_ERR_INVALID;                         \
+    return index_and_shift<T>(a, idx, out, out_shift, ncol, n, m, pitch_a, pitch_idx, pitch_out, cm, shift_by, \
+                              ST(s));                                                                          \
+  }                                                                                                            \
+  int ekat_b200_transpose3_##sfx(const T* src, T* dst, int64_t ni, int nk, int nj, int64_t c_stride,           \
+                                 int64_t f_pitch, int c2f, ekat_b200_stream_t s) {                             \
+    if (ni < 0 || nk < 0 || nj < 0 || c_stride < (int64_t)nk * nj || f_pitch < ni) return EKAT_B200_ERR_INVALID; \
+    if (ni && nk && nj && (!src || !dst || src == dst)) return EKAT_B200_ERR_INVALID;                          \
+    return transpose3<T>(src, dst, ni, nk, nj, c_stride, f_pitch, c2f, ST(s));                                 \
+  }                                                                                                            \
+  int ekat_b200_repack_##sfx(const T* src, T* dst, int64_t nrows, int n, int64_t src_stride, int64_t dst_pitch, \
+                             int zero_pad, ekat_b200_stream_t s) {                                             \
+    if (nrows < 0 || n < 0 || src_stride < n || dst_pitch < n) return EKAT_B200_ERR_INVALID;                   \
+    if (nrows && n && (!src || !dst || src == dst)) return EKAT_B200_ERR_INVALID;                              \
+    return repack<T>(src, dst, nrows, n, src_stride, dst_pitch, zero_pad, ST(s));                              \
   }                                                                                                            \
   int ekat_b200_view_reduction_##sfx(const T* in, T* out, int64_t ncol, int begin, int end, int64_t pitch,     \
                                      ekat_b200_layout layout, int pack_n, ekat_b200_stream_t s) {             \

@@ -1,4 +1,5 @@
-// column_ops.cu -- ekat::adj_diff for every index of every column of a batch.
+// column_ops.cu -- the column-ops neighbours of the Pack glue for every column of a batch:
+// ekat::adj_diff, ekat::shift_left / shift_right, ekat::index_and_shift.
 //
 // Replaces the per-column, per-index loop around ekat::adj_diff<Forward>(view, index, index_end) (reference
 // src/pack/ekat_pack_kokkos.hpp:100-164; call form tests/pack/pack_kokkos_utils.cpp:1055-1080) -- the finite-difference
@@ -122,6 +123,104 @@ int adj_diff(const R* in, R* out, int64_t ncol, int n, int64_t pitch_in, int64_t
   return check_cuda(cudaGetLastError());
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// ekat::shift_right / ekat::shift_left over a whole column (reference src/pack/ekat_pack.hpp:521-555): applied pack
+// after pack along a scalarized column, shift_right(v(k-1), v(k)) moves every scalar one place up the column and
+// shift_left(v(k+1), v(k)) one place down, the first / last place taking the scalar `fill` (the ScalarType overloads,
+// :531-538, :549-555 -- what adj_diff passes at the ends, ekat_pack_kokkos.hpp:119,124). Generalised to any shift s:
+//   out[k] = (0 <= k - s < n) ? in[k - s] : fill        s = +1: shift_right, s = -1: shift_left
+// A copy, so bit-identical by construction. Roofline: HBM, 2 * n * word bytes per column.
+template <typename R, bool COLMAJ>
+__global__ void __launch_bounds__(256)
+k_shift(const R* __restrict__ in, R* __restrict__ out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out, int shift,
+        R fill) {
+  const int64_t total = ncol * n;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
+    int64_t c;
+    int k;
+    if (COLMAJ) {  // lanes along the column: element (c, k) at c*pitch + k
+      c = i / n;
+      k = (int)(i - c * n);
+    } else {  // lanes along the batch: element (c, k) at k*pitch + c
+      k = (int)(i / ncol);
+      c = i - (int64_t)k * ncol;
+    }
+    const int ks = k - shift;
+    const bool ok = ks >= 0 && ks < n;
+    const size_t src = COLMAJ ? (size_t)c * pitch_in + (ok ? ks : 0) : (size_t)(ok ? ks : 0) * pitch_in + c;
+    const size_t dst = COLMAJ ? (size_t)c * pitch_out + k : (size_t)k * pitch_out + c;
+    const R v = ld_stream(in + src);
+    st_stream(out + dst, ok ? v : fill);
+  }
+}
+
+template <typename R>
+int shift(const R* in, R* out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out, int col_major, int s, R fill,
+          cudaStream_t st) {
+  if (ncol == 0 || n == 0) return EKAT_B200_OK;
+  const int64_t total = ncol * n;
+  const unsigned blocks = (unsigned)tmin<int64_t>((total + 255) / 256, (int64_t)kNumSms * 8 * 16);
+  if (col_major) k_shift<R, true><<<blocks, 256, 0, st>>>(in, out, ncol, n, pitch_in, pitch_out, s, fill);
+  else k_shift<R, false><<<blocks, 256, 0, st>>>(in, out, ncol, n, pitch_in, pitch_out, s, fill);
+  note_launch(sizeof(R) == 8 ? "shift<f64>" : "shift<f32>");
+  return check_cuda(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// ekat::index_and_shift<Shift>(a, idx, index, index_shift) for every index pack of every column (reference
+// src/pack/ekat_pack_kokkos.hpp:71-98; the gather pair y1(k1), y1(k1+1) of a column remap):
+//   out[c][j] = a[c][idx[c][j]],   out_shift[c][j] = a[c][idx[c][j] + shift]
+// Where idx or idx + shift falls outside [0, n) the reference's release build reads out of bounds; its debug build
+// leaves `index` as the caller had it and sets `index_shift` to ekat::invalid (a quiet NaN, :85-93) -- that defined
+// behaviour is the one kept here. Gathered copies: bit-identical by construction.
+// Roofline: HBM, (n + m) * word + m * 4 bytes read and 2 * m * word bytes written per column (a is read once: the
+// gathers of a column hit L1/L2).
+template <typename R, bool COLMAJ>
+__global__ void __launch_bounds__(256)
+k_index_and_shift(const R* __restrict__ a, const int* __restrict__ idx, R* __restrict__ out, R* __restrict__ out_shift,
+                  int64_t ncol, int n, int m, int64_t pitch_a, int64_t pitch_idx, int64_t pitch_out, int shift) {
+  const int64_t total = ncol * m;
+  const R invalid = sizeof(R) == 8 ? (R)__longlong_as_double(0x7ff8000000000000ll) : (R)__int_as_float(0x7fc00000);
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
+    int64_t c;
+    int j;
+    if (COLMAJ) {
+      c = i / m;
+      j = (int)(i - c * m);
+    } else {
+      j = (int)(i / ncol);
+      c = i - (int64_t)j * ncol;
+    }
+    const size_t io = COLMAJ ? (size_t)c * pitch_idx + j : (size_t)j * pitch_idx + c;
+    const size_t oo = COLMAJ ? (size_t)c * pitch_out + j : (size_t)j * pitch_out + c;
+    const int k = __ldg(idx + io), ks = k + shift;
+    if (k >= 0 && k < n && ks >= 0 && ks < n) {
+      const size_t a0 = COLMAJ ? (size_t)c * pitch_a + k : (size_t)k * pitch_a + c;
+      const size_t a1 = COLMAJ ? (size_t)c * pitch_a + ks : (size_t)ks * pitch_a + c;
+      out[oo] = __ldg(a + a0);
+      out_shift[oo] = __ldg(a + a1);
+    } else {
+      out_shift[oo] = invalid;
+    }
+  }
+}
+
+template <typename R>
+int index_and_shift(const R* a, const int* idx, R* out, R* out_shift, int64_t ncol, int n, int m, int64_t pitch_a,
+                    int64_t pitch_idx, int64_t pitch_out, int col_major, int s, cudaStream_t st) {
+  if (ncol == 0 || m == 0) return EKAT_B200_OK;
+  const int64_t total = ncol * m;
+  const unsigned blocks = (unsigned)tmin<int64_t>((total + 255) / 256, (int64_t)kNumSms * 8 * 16);
+  if (col_major) k_index_and_shift<R, true><<<blocks, 256, 0, st>>>(a, idx, out, out_shift, ncol, n, m, pitch_a, pitch_idx, pitch_out, s);
+  else k_index_and_shift<R, false><<<blocks, 256, 0, st>>>(a, idx, out, out_shift, ncol, n, m, pitch_a, pitch_idx, pitch_out, s);
+  note_launch(sizeof(R) == 8 ? "index_and_shift<f64>" : "index_and_shift<f32>");
+  return check_cuda(cudaGetLastError());
+}
+
+template int shift<double>(const double*, double*, int64_t, int, int64_t, int64_t, int, int, double, cudaStream_t);
+template int shift<float>(const float*, float*, int64_t, int, int64_t, int64_t, int, int, float, cudaStream_t);
+template int index_and_shift<double>(const double*, const int*, double*, double*, int64_t, int, int, int64_t, int64_t, int64_t, int, int, cudaStream_t);
+template int index_and_shift<float>(const float*, const int*, float*, float*, int64_t, int, int, int64_t, int64_t, int64_t, int, int, cudaStream_t);
 template int adj_diff<double>(const double*, double*, int64_t, int, int64_t, int64_t, int, int, cudaStream_t);
 template int adj_diff<float>(const float*, float*, int64_t, int, int64_t, int64_t, int, int, cudaStream_t);
 

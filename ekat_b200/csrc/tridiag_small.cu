@@ -38,7 +38,10 @@ constexpr int kSmallGroups = 3;  // TMA boxes per plane
 // UP = true: the bottom half, levels descending from nlev-1 (the same recurrence on the reversed system: du plays
 // dl's part and vice versa). Chunks [kfirst, kfirst + nk) of 8 levels in processing order; within a chunk, slot
 // s = 0..7 is level k*8 + s (top) or k*8 + 7 - s (bottom), so both halves run identical code on slot-ordered registers.
-template <typename R, int RN, bool UP>
+// MODE 0: the matrix is given (dl, d, du planes). MODE 1: the matrix is the implicit-diffusion stencil built on the
+// fly from the exchange coefficients w (in the sdu plane, see k_tridiag_small): dl[i] = -w[i-1], du[i] = -w[i],
+// d[i] = 1 + w[i] + w[i-1] -- sdl is unused and q overwrites the coordinate plane.
+template <typename R, int RN, bool UP, int MODE>
 __device__ __forceinline__ void small_half(R* __restrict__ sdl, R* __restrict__ sd, R* __restrict__ sdu, R* __restrict__ sx,
                                            uint64_t* bar, R* xch, int lane, int nlev, int nch, int gch, int kt, R* __restrict__ gx,
                                            int64_t x_stride, bool full_tile, bool live) {
@@ -55,12 +58,19 @@ __device__ __forceinline__ void small_half(R* __restrict__ sdl, R* __restrict__ 
     for (int s = 0; s < LB; ++s) {
       const int i = lev_of(k, s);
       const size_t o = (size_t)i * 32 + lane;
-      ra[s] = UP ? sdu[o] : sdl[o];
-      rb[s] = sd[o];
-      rc[s] = UP ? sdl[o] : sdu[o];
+      if (MODE == 1) {
+        const R wi = sdu[o], wm = i > 0 ? sdu[o - 32] : (R)0;  // w[-1] = w[n-1] = 0: the unused ends vanish by themselves
+        ra[s] = UP ? -wi : -wm;
+        rc[s] = UP ? -wm : -wi;
+        rb[s] = x_add(x_add((R)1, wi), wm);
+      } else {
+        ra[s] = UP ? sdu[o] : sdl[o];
+        rb[s] = sd[o];
+        rc[s] = UP ? sdl[o] : sdu[o];
+      }
       rx[s] = sx[o];
-      if (i == 0) (UP ? rc[s] : ra[s]) = (R)0;
-      if (i == nlev - 1) (UP ? ra[s] : rc[s]) = (R)0;
+      if (MODE == 0 && i == 0) (UP ? rc[s] : ra[s]) = (R)0;
+      if (MODE == 0 && i == nlev - 1) (UP ? ra[s] : rc[s]) = (R)0;
       if (i >= nlev) {
         ra[s] = (R)0;
         rb[s] = (R)1;
@@ -158,7 +168,8 @@ __device__ __forceinline__ void small_half(R* __restrict__ sdl, R* __restrict__ 
       const size_t o = (size_t)i * 32 + lane;
       rq[s] = sd[o];
       rz[s] = sx[o];
-      ru[s] = UP ? sdl[o] : sdu[o];
+      if (MODE == 1) ru[s] = UP ? (i > 0 ? -sdu[o - 32] : (R)0) : -sdu[o];
+      else ru[s] = UP ? sdl[o] : sdu[o];
       if (i == (UP ? 0 : nlev - 1) || i >= nlev) ru[s] = (R)0;
     }
   };
@@ -197,7 +208,7 @@ __device__ __forceinline__ void small_half(R* __restrict__ sdl, R* __restrict__ 
   }
 }
 
-template <typename R, int RN>
+template <typename R, int RN, int MODE>
 __global__ void __launch_bounds__(64)
 k_tridiag_small(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
                 const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mx, R* __restrict__ X, int64_t ncol,
@@ -213,10 +224,11 @@ k_tridiag_small(const __grid_constant__ CUtensorMap mdl, const __grid_constant__
   R* xch = reinterpret_cast<R*>(smem_raw + 128);       // interface exchange: [half][y | c][lane]
   R* P = reinterpret_cast<R*>(smem_raw + 128 + 1024);
   const size_t plane = (size_t)ngrp * GL * 32;
+  // MODE 1 has no dl plane: md = the level coordinate z (its plane receives q), mdu = kd (its plane receives w)
   R* sdl = P;
-  R* sd = P + plane;
-  R* sdu = P + 2 * plane;
-  R* sx = P + 3 * plane;
+  R* sd = MODE == 1 ? P : P + plane;
+  R* sdu = sd + plane;
+  R* sx = sdu + plane;
   const int c0 = blockIdx.x * 32;
   const int row0 = blockIdx.y * nlev;
 
@@ -227,9 +239,9 @@ k_tridiag_small(const __grid_constant__ CUtensorMap mdl, const __grid_constant__
     for (int i = 0; i < ngrp; ++i) {
       const int g = (i & 1) ? ngrp - 1 - i / 2 : i / 2;  // outermost groups first: both halves start at once
       // a box past the last level of this matrix reads rows of the next one (or zeros past the array): neutralised at staging
-      mbar_expect_tx(&bar[g], 4u * (unsigned)GL * 32u * (unsigned)sizeof(R));
+      mbar_expect_tx(&bar[g], (MODE == 1 ? 3u : 4u) * (unsigned)GL * 32u * (unsigned)sizeof(R));
       const size_t o = (size_t)g * GL * 32;
-      tma_load_2d_hint(sdl + o, &mdl, c0, row0 + g * GL, &bar[g], pol);
+      if (MODE == 0) tma_load_2d_hint(sdl + o, &mdl, c0, row0 + g * GL, &bar[g], pol);
       tma_load_2d_hint(sd + o, &md, c0, row0 + g * GL, &bar[g], pol);
       tma_load_2d_hint(sdu + o, &mdu, c0, row0 + g * GL, &bar[g], pol);
       tma_load_2d_hint(sx + o, &mx, c0, row0 + g * GL, &bar[g], pol);
@@ -237,27 +249,40 @@ k_tridiag_small(const __grid_constant__ CUtensorMap mdl, const __grid_constant__
   }
   __syncthreads();  // barrier initialisation visible to both warps
 
+  if (MODE == 1) {
+    // the finite-difference step, fused: w[i] = kd[i] / (z[i+1] - z[i]) -- ekat::adj_diff<Forward> (reference
+    // src/pack/ekat_pack_kokkos.hpp:139-152) followed by the caller's coefficient formula -- for every level of the
+    // tile, in place over kd (one IEEE division each, so the implied matrix is bit-defined); w[n-1] = 0.
+    for (int g = 0; g < ngrp; ++g) mbar_wait(&bar[g], 0u);
+    for (int i = warp; i < nch * LB; i += 2) {
+      const size_t o = (size_t)i * 32 + lane;
+      const R dz = i < nlev - 1 ? x_sub(sd[o + 32], sd[o]) : (R)1;
+      sdu[o] = i < nlev - 1 ? x_div(sdu[o], dz) : (R)0;
+    }
+    __syncthreads();
+  }
   const bool full_tile = (int64_t)c0 + 32 <= ncol, live = (int64_t)c0 + lane < ncol;
   R* gx = X + (size_t)row0 * x_stride + c0 + lane;
-  if (warp == 0) small_half<R, RN, false>(sdl, sd, sdu, sx, bar, xch, lane, nlev, nch, gch, kt, gx, x_stride, full_tile, live);
-  else if (kt < nch) small_half<R, RN, true>(sdl, sd, sdu, sx, bar, xch, lane, nlev, nch, gch, kt, gx, x_stride, full_tile, live);
+  if (warp == 0) small_half<R, RN, false, MODE>(sdl, sd, sdu, sx, bar, xch, lane, nlev, nch, gch, kt, gx, x_stride, full_tile, live);
+  else if (kt < nch) small_half<R, RN, true, MODE>(sdl, sd, sdu, sx, bar, xch, lane, nlev, nch, gch, kt, gx, x_stride, full_tile, live);
 }
 
 // Level-major operands: dl,d,du [nmat][nlev][a_stride], X [nmat][nlev][x_stride]. Returns EKAT_B200_ERR_UNSUPPORTED
-// when the operands do not meet TMA's requirements or fewer than two tiles would fit an SM (the caller then uses
-// the pipelined kernels); `force` (tuning) skips the residency test as long as one tile fits.
-template <typename R>
-int tridiag_small(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride, bool force,
-                  cudaStream_t stream) {
+// when the operands do not meet TMA's requirements or the batch is not one this kernel wins on (the caller then
+// uses the pipelined kernels); `force` (tuning) skips that test as long as one tile fits.
+// MODE 1: d = level coordinate z, du = kd (dl unused), one matrix and one right-hand side per column.
+template <typename R, int MODE>
+static int run_small(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride, bool force,
+                     cudaStream_t stream) {
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
-  if (!al(dl) || !al(d) || !al(du) || !al(X) || (a_stride * sizeof(R)) % 16 || (x_stride * sizeof(R)) % 16)
+  if ((MODE == 0 && !al(dl)) || !al(d) || !al(du) || !al(X) || (a_stride * sizeof(R)) % 16 || (x_stride * sizeof(R)) % 16)
     return EKAT_B200_ERR_UNSUPPORTED;
   if (ncol >= (int64_t)1 << 31 || (int64_t)nmat * nlev >= (int64_t)1 << 31 || nmat > 65535) return EKAT_B200_ERR_UNSUPPORTED;
   const int nch = (nlev + kLB - 1) / kLB;
   const int gch = (nch + kSmallGroups - 1) / kSmallGroups, GL = gch * kLB;  // levels per TMA box (<= 256)
   if (GL > 256) return EKAT_B200_ERR_UNSUPPORTED;
   const int ngrp = (nlev + GL - 1) / GL;
-  const size_t smem = 128 + 1024 + 4 * (size_t)ngrp * GL * 32 * sizeof(R);
+  const size_t smem = 128 + 1024 + (MODE == 1 ? 3 : 4) * (size_t)ngrp * GL * 32 * sizeof(R);
   if (smem > kMaxSmemPerCta) return EKAT_B200_ERR_UNSUPPORTED;
   // Measured (profiles/r02_small_batches.txt): with >= 3 tiles per SM and at most two waves of tiles this kernel wins
   // (21,600 x 72 f64: 11.1 us against 13.0-14.1 us); longer columns (128 levels: 2-3 tiles per SM at best) and larger
@@ -267,19 +292,75 @@ int tridiag_small(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, in
   if (!force && (per_sm < 3 || nlev > 96 || tiles > (int64_t)2 * kNumSms * per_sm)) return EKAT_B200_ERR_UNSUPPORTED;
   CUtensorMap mdl, md, mdu, mx;
   const int64_t rows = (int64_t)nmat * nlev;
-  if (!make_tensor_map_2d<R>(&mdl, dl, ncol, rows, a_stride, 32, GL, 0) || !make_tensor_map_2d<R>(&md, d, ncol, rows, a_stride, 32, GL, 0) ||
-      !make_tensor_map_2d<R>(&mdu, du, ncol, rows, a_stride, 32, GL, 0) || !make_tensor_map_2d<R>(&mx, X, ncol, rows, x_stride, 32, GL, 0))
+  if (!make_tensor_map_2d<R>(&md, d, ncol, rows, a_stride, 32, GL, 0) || !make_tensor_map_2d<R>(&mdu, du, ncol, rows, a_stride, 32, GL, 0) ||
+      !make_tensor_map_2d<R>(&mx, X, ncol, rows, x_stride, 32, GL, 0))
     return EKAT_B200_ERR_UNSUPPORTED;
-  auto k = k_tridiag_small<R, TmaCfg<R>::RN>;
+  if (MODE == 0) {
+    if (!make_tensor_map_2d<R>(&mdl, dl, ncol, rows, a_stride, 32, GL, 0)) return EKAT_B200_ERR_UNSUPPORTED;
+  } else {
+    mdl = md;
+  }
+  auto k = k_tridiag_small<R, TmaCfg<R>::RN, MODE>;
   int rc = allow_smem(k, smem);
   if (rc) return rc;
   dim3 grid((unsigned)((ncol + 31) / 32), (unsigned)nmat);
   k<<<grid, 64, smem, stream>>>(mdl, md, mdu, mx, X, ncol, nlev, x_stride, GL);
-  note_launch(sizeof(R) == 8 ? "tridiag_small<f64,thomas>" : "tridiag_small<f32,thomas>");
+  note_launch(MODE == 1 ? (sizeof(R) == 8 ? "diffusion_solve<f64>" : "diffusion_solve<f32>")
+                        : (sizeof(R) == 8 ? "tridiag_small<f64,thomas>" : "tridiag_small<f32,thomas>"));
+  return check_cuda(cudaGetLastError());
+}
+
+template <typename R>
+int tridiag_small(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride, bool force,
+                  cudaStream_t stream) {
+  return run_small<R, 0>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, force, stream);
+}
+
+// The fused "difference -> (dl, d, du) -> solve" step: z, kd [nlev][pitch] level-major, X
+// [nlev][pitch] in/out. EKAT_B200_ERR_UNSUPPORTED when the operands do not meet TMA's requirements or a tile of
+// 3 planes x nlev x 32 columns does not fit on chip.
+template <typename R>
+int diffusion_solve(const R* z, const R* kd, R* X, int64_t ncol, int nlev, int64_t pitch, cudaStream_t stream) {
+  return run_small<R, 1>(nullptr, const_cast<R*>(z), const_cast<R*>(kd), X, ncol, nlev, 1, pitch, pitch, true, stream);
+}
+
+// The same stencil unfused: writes the matrix the fused kernel implies (for callers that want it, and as the two-pass
+// baseline the fusion is measured against): w[i] = kd[i] / (z[i+1] - z[i]); dl[i] = -w[i-1]; du[i] = -w[i];
+// d[i] = (1 + w[i]) + w[i-1]; w[-1] = w[n-1] = 0. One thread per column, rows coalesced.
+template <typename R>
+__global__ void __launch_bounds__(128)
+k_diffusion_matrix(const R* __restrict__ z, const R* __restrict__ kd, R* __restrict__ dl, R* __restrict__ d, R* __restrict__ du,
+                   int64_t ncol, int nlev, int64_t pitch) {
+  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ncol) return;
+  R wm = (R)0, zi = ld_stream(z + c);
+  for (int i = 0; i < nlev; ++i) {
+    const size_t o = (size_t)i * pitch + c;
+    R wi = (R)0, zn = zi;
+    if (i < nlev - 1) {
+      zn = ld_stream(z + o + pitch);
+      wi = x_div(ld_stream(kd + o), x_sub(zn, zi));
+    }
+    st_stream(dl + o, -wm);
+    st_stream(du + o, -wi);
+    st_stream(d + o, x_add(x_add((R)1, wi), wm));
+    wm = wi;
+    zi = zn;
+  }
+}
+template <typename R>
+int diffusion_matrix(const R* z, const R* kd, R* dl, R* d, R* du, int64_t ncol, int nlev, int64_t pitch, cudaStream_t stream) {
+  if (ncol == 0) return EKAT_B200_OK;
+  k_diffusion_matrix<R><<<(unsigned)((ncol + 127) / 128), 128, 0, stream>>>(z, kd, dl, d, du, ncol, nlev, pitch);
+  note_launch("diffusion_matrix");
   return check_cuda(cudaGetLastError());
 }
 
 template int tridiag_small<double>(double*, double*, double*, double*, int64_t, int, int, int64_t, int64_t, bool, cudaStream_t);
 template int tridiag_small<float>(float*, float*, float*, float*, int64_t, int, int, int64_t, int64_t, bool, cudaStream_t);
+template int diffusion_solve<double>(const double*, const double*, double*, int64_t, int, int64_t, cudaStream_t);
+template int diffusion_solve<float>(const float*, const float*, float*, int64_t, int, int64_t, cudaStream_t);
+template int diffusion_matrix<double>(const double*, const double*, double*, double*, double*, int64_t, int, int64_t, cudaStream_t);
+template int diffusion_matrix<float>(const float*, const float*, float*, float*, float*, int64_t, int, int64_t, cudaStream_t);
 
 }  // namespace ekb

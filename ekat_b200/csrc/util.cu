@@ -131,6 +131,60 @@ __global__ void k_lev_to_col(const R* __restrict__ src, R* __restrict__ dst, int
   }
 }
 
+// ekat::transpose<c2f | f2c> for rank-3 arrays (reference src/kokkos/ekat_math_utils.hpp:124-147), on the device and
+// with pitches: the C side is [ni][nk][nj] (element (i,k,j) at c[i*c_stride + k*nj + j]; the reference's batch layout
+// X[col][lev][rhs]), the Fortran side [nj][nk][ni] (element at f[(j*nk + k)*f_pitch + i]; the native level-major layout
+// X[rhs][lev][col]). With q = k*nj + j the C side is a 2-D array [ni][nk*nj], so one 32 x 32 tile through padded
+// shared memory serves: rows of q are contiguous on the C side, rows of i on the Fortran side (row (q % nj)*nk + q / nj).
+// Roofline: HBM, 2 * word bytes per element.
+template <typename R, bool C2F>
+__global__ void k_transpose3(const R* __restrict__ src, R* __restrict__ dst, int64_t ni, int nk, int nj, int64_t c_stride,
+                             int64_t f_pitch) {
+  __shared__ R tile[32][33];
+  const int64_t i0 = (int64_t)blockIdx.x * 32;
+  const int q0 = blockIdx.y * 32, nq = nk * nj;
+  if (C2F) {
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+      const int64_t i = i0 + r;
+      const int q = q0 + threadIdx.x;
+      if (i < ni && q < nq) tile[r][threadIdx.x] = ld_stream(src + (size_t)i * c_stride + q);
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+      const int q = q0 + r;
+      const int64_t i = i0 + threadIdx.x;
+      if (i < ni && q < nq) st_stream(dst + ((size_t)(q % nj) * nk + q / nj) * f_pitch + i, tile[threadIdx.x][r]);
+    }
+  } else {
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+      const int q = q0 + r;
+      const int64_t i = i0 + threadIdx.x;
+      if (i < ni && q < nq) tile[r][threadIdx.x] = ld_stream(src + ((size_t)(q % nj) * nk + q / nj) * f_pitch + i);
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+      const int64_t i = i0 + r;
+      const int q = q0 + threadIdx.x;
+      if (i < ni && q < nq) st_stream(dst + (size_t)i * c_stride + q, tile[threadIdx.x][r]);
+    }
+  }
+}
+
+// Row repacking of the host_to_device / device_to_host family (reference src/pack/ekat_pack_kokkos.hpp:332-1035): a
+// rank-2 scalar array [nrows][n] (row stride src_stride) becomes the scalarized storage of a view of Pack<R,N> rows,
+// [nrows][npack*N] (row stride dst_pitch >= n), the padding lanes zero as a freshly allocated Kokkos view has them
+// (zero_pad), or left alone; with dst_pitch == n it is the reverse direction (device_to_host drops the padding).
+template <typename R>
+__global__ void __launch_bounds__(256)
+k_repack(const R* __restrict__ src, R* __restrict__ dst, int64_t nrows, int n, int64_t src_stride, int64_t dst_pitch, int width) {
+  const int64_t total = nrows * width;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
+    const int64_t r = i / width;
+    const int k = (int)(i - r * width);
+    st_stream(dst + (size_t)r * dst_pitch + k, k < n ? ld_stream(src + (size_t)r * src_stride + k) : (R)0);
+  }
+}
+
 // ------------------------------------------------------------------------ reductions
 template <typename R> struct Bits;
 template <> struct Bits<double> { static __device__ uint64_t of(double v) { return (uint64_t)__double_as_longlong(v); } };
@@ -282,6 +336,27 @@ int lev_to_col(const R* src, R* dst, int64_t ncol, int n, int64_t pitch, int64_t
   return check_cuda(cudaGetLastError());
 }
 template <typename R>
+int transpose3(const R* src, R* dst, int64_t ni, int nk, int nj, int64_t c_stride, int64_t f_pitch, int c2f, cudaStream_t st) {
+  if (ni == 0 || nk == 0 || nj == 0) return EKAT_B200_OK;
+  const int64_t nq = (int64_t)nk * nj;
+  if (nq >= (int64_t)65535 * 32) return EKAT_B200_ERR_TOO_LARGE;
+  dim3 grid((unsigned)((ni + 31) / 32), (unsigned)((nq + 31) / 32)), block(32, 8);
+  if (c2f) k_transpose3<R, true><<<grid, block, 0, st>>>(src, dst, ni, nk, nj, c_stride, f_pitch);
+  else k_transpose3<R, false><<<grid, block, 0, st>>>(src, dst, ni, nk, nj, c_stride, f_pitch);
+  note_launch(c2f ? "transpose3_c2f" : "transpose3_f2c");
+  return check_cuda(cudaGetLastError());
+}
+template <typename R>
+int repack(const R* src, R* dst, int64_t nrows, int n, int64_t src_stride, int64_t dst_pitch, int zero_pad, cudaStream_t st) {
+  if (nrows == 0 || n == 0) return EKAT_B200_OK;
+  const int width = zero_pad ? (int)dst_pitch : n;
+  const int64_t total = nrows * width;
+  const unsigned blocks = (unsigned)tmin<int64_t>((total + 255) / 256, (int64_t)kNumSms * 8 * 16);
+  k_repack<R><<<blocks, 256, 0, st>>>(src, dst, nrows, n, src_stride, dst_pitch, width);
+  note_launch("repack");
+  return check_cuda(cudaGetLastError());
+}
+template <typename R>
 int checksum(const R* a, int64_t nrows, int64_t ncol, int64_t pitch, uint64_t* out, cudaStream_t st) {
   if (nrows * ncol == 0) return EKAT_B200_OK;
   const int64_t total = nrows * ncol;
@@ -307,6 +382,8 @@ int residual(const R* dl, const R* d, const R* du, const R* B, const R* X, int64
                                   cudaStream_t);                                                             \
   template int col_to_lev<R>(const R*, R*, int64_t, int, int64_t, int64_t, cudaStream_t);                    \
   template int lev_to_col<R>(const R*, R*, int64_t, int, int64_t, int64_t, cudaStream_t);                    \
+  template int transpose3<R>(const R*, R*, int64_t, int, int, int64_t, int64_t, int, cudaStream_t);          \
+  template int repack<R>(const R*, R*, int64_t, int, int64_t, int64_t, int, cudaStream_t);                   \
   template int checksum<R>(const R*, int64_t, int64_t, int64_t, uint64_t*, cudaStream_t);                    \
   template int residual<R>(const R*, const R*, const R*, const R*, const R*, int64_t, int, int, int, int64_t, \
                            double*, cudaStream_t);

@@ -65,3 +65,58 @@ def adj_diff(x, forward=True, layout=COL_MAJOR, ncol=None, out=None):
     check(fn, getattr(lib(), fn)(x.data_ptr(), out.data_ptr(), nc, n, pin, pout, layout, 1 if forward else 0,
                                  torch.cuda.current_stream().cuda_stream))
     return out
+
+
+def _dims(x, layout, ncol):
+    """(ncol, n, pitch) of a 2-D operand in either layout."""
+    if layout == COL_MAJOR:
+        nc, n = x.shape
+        return nc, n, (x.stride(0) if nc > 1 else n)
+    n, width = x.shape
+    return (width if ncol is None else ncol), n, (x.stride(0) if n > 1 else width)
+
+
+def shift(x, shift_by, fill=0.0, layout=COL_MAJOR, ncol=None, out=None):
+    """ekat::shift_right (shift_by = +1) / ekat::shift_left (-1) applied pack after pack along every (scalarized) column
+    (reference src/pack/ekat_pack.hpp:521-555): out[k] = x[k - shift_by], `fill` where that falls off the column.
+    COL_MAJOR x [ncol, n] (dim-0 may be strided); LEV_MAJOR x [n, pitch]."""
+    if not x.is_cuda or x.dtype not in _SFX or x.dim() != 2 or (x.numel() > 0 and x.shape[1] > 1 and x.stride(1) != 1):
+        raise ValueError("shift needs a 2-D float32/float64 CUDA tensor with unit last stride (no CPU path)")
+    if out is None:
+        out = torch.empty(x.shape, dtype=x.dtype, device=x.device)
+    if out.shape != x.shape or out.dtype != x.dtype or (out.numel() > 0 and out.shape[1] > 1 and out.stride(1) != 1):
+        raise ValueError("shift: out must match x")
+    nc, n, pin = _dims(x, layout, ncol)
+    _, _, pout = _dims(out, layout, ncol)
+    fn = f"ekat_b200_shift_{_SFX[x.dtype]}"
+    check(fn, getattr(lib(), fn)(x.data_ptr(), out.data_ptr(), nc, n, pin, pout, layout, int(shift_by), float(fill),
+                                 torch.cuda.current_stream().cuda_stream))
+    return out
+
+
+def index_and_shift(a, idx, shift_by, layout=COL_MAJOR, ncol=None, out=None, out_shift=None):
+    """ekat::index_and_shift<shift_by> for every index of every column (reference src/pack/ekat_pack_kokkos.hpp:71-98):
+    out[j] = a[idx[j]], out_shift[j] = a[idx[j] + shift_by]; where an index leaves the column, out[j] is left as it was
+    and out_shift[j] is NaN (the reference's debug-build behaviour). a [ncol, n] / idx [ncol, m] int32 (COL_MAJOR) or
+    a [n, pitch] / idx [m, pitch] (LEV_MAJOR). Returns (out, out_shift)."""
+    if not a.is_cuda or a.dtype not in _SFX or a.dim() != 2 or not idx.is_cuda or idx.dtype != torch.int32 or idx.dim() != 2:
+        raise ValueError("index_and_shift needs a 2-D float CUDA tensor and a 2-D int32 CUDA index tensor (no CPU path)")
+    for t in (a, idx):
+        if t.numel() > 0 and t.shape[1] > 1 and t.stride(1) != 1:
+            raise ValueError("index_and_shift: unit last stride required")
+    if out is None:
+        out = torch.zeros(idx.shape, dtype=a.dtype, device=a.device)
+    if out_shift is None:
+        out_shift = torch.zeros(idx.shape, dtype=a.dtype, device=a.device)
+    for t in (out, out_shift):
+        if t.shape != idx.shape or t.dtype != a.dtype or not t.is_contiguous():
+            raise ValueError("index_and_shift: outputs must be contiguous and shaped like idx")
+    nc, n, pa = _dims(a, layout, ncol)
+    nci, m, pi = _dims(idx, layout, ncol)
+    if nci != nc:
+        raise ValueError("a and idx disagree on the number of columns")
+    _, _, po = _dims(out, layout, ncol)
+    fn = f"ekat_b200_index_and_shift_{_SFX[a.dtype]}"
+    check(fn, getattr(lib(), fn)(a.data_ptr(), idx.data_ptr(), out.data_ptr(), out_shift.data_ptr(), nc, n, m, pa, pi, po,
+                                 layout, int(shift_by), torch.cuda.current_stream().cuda_stream))
+    return out, out_shift

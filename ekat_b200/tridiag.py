@@ -164,3 +164,65 @@ def fill(dtype, ncol, nlev, nA, nrhs, layout=LEV_MAJOR, col0=0, seed_mod=32768, 
     check(fn, getattr(lib(), fn)(dl.data_ptr(), d.data_ptr(), du.data_ptr(), X.data_ptr(), ncol, col0, nlev, nA, nrhs,
                                  a_stride, x_stride, layout, seed_mod, _stream()))
     return dl, d, du, X
+
+
+def transpose3(src, c2f=True, f_pitch=None, ni=None, out=None):
+    """ekat::transpose<c2f|f2c> for rank-3 arrays on the device (reference src/kokkos/ekat_math_utils.hpp:124-147).
+    c2f: src [ni, nk, nj] (dim-0 may be strided, e.g. the reference batch X[col][lev][rhs]) -> [nj, nk, f_pitch]
+    (the native X[rhs][lev][col]); f2c: src [nj, nk, pitch] -> [ni, nk, nj]."""
+    fn = f"ekat_b200_transpose3_{_SFX[src.dtype]}"
+    if c2f:
+        n_i, nk, nj = src.shape
+        _require(src.stride(2) == 1 and src.stride(1) == nj, "transpose3: C side must be [ni][nk*nj] rows")
+        f_pitch = n_i if f_pitch is None else f_pitch
+        dst = torch.empty((nj, nk, f_pitch), dtype=src.dtype, device=src.device) if out is None else out
+        _require(dst.shape == (nj, nk, f_pitch) and dst.is_contiguous() and dst.dtype == src.dtype, "transpose3: out")
+        check(fn, getattr(lib(), fn)(src.data_ptr(), dst.data_ptr(), n_i, nk, nj, src.stride(0) if n_i > 1 else nk * nj,
+                                     f_pitch, 1, _stream()))
+    else:
+        nj, nk, pitch = src.shape
+        _require(src.is_contiguous(), "transpose3: Fortran side must be contiguous [nj][nk][pitch]")
+        n_i = pitch if ni is None else ni
+        dst = torch.empty((n_i, nk, nj), dtype=src.dtype, device=src.device) if out is None else out
+        _require(dst.shape == (n_i, nk, nj) and dst.is_contiguous() and dst.dtype == src.dtype, "transpose3: out")
+        check(fn, getattr(lib(), fn)(src.data_ptr(), dst.data_ptr(), n_i, nk, nj, nk * nj, pitch, 0, _stream()))
+    return dst
+
+
+def repack(src, pitch, zero_pad=True):
+    """Row repacking of host_to_device / device_to_host (reference src/pack/ekat_pack_kokkos.hpp:332-1035):
+    [nrows, n] scalars -> [nrows, pitch] (pitch = npack*N >= n), padding lanes zero if zero_pad."""
+    nrows, n = src.shape
+    _require(src.stride(1) == 1 and pitch >= n, "repack: unit last stride and pitch >= n")
+    dst = torch.empty((nrows, pitch), dtype=src.dtype, device=src.device)
+    fn = f"ekat_b200_repack_{_SFX[src.dtype]}"
+    check(fn, getattr(lib(), fn)(src.data_ptr(), dst.data_ptr(), nrows, n, src.stride(0) if nrows > 1 else n, pitch,
+                                 1 if zero_pad else 0, _stream()))
+    return dst
+
+
+def diffusion_solve(z, kd, X, ncol=None):
+    """Fused adj_diff -> (dl, d, du) -> thomas for the implicit vertical-diffusion stencil (ekat_b200.h): z, kd, X
+    [nlev, pitch] level-major, X overwritten with the solution. The diagonals never touch HBM."""
+    nlev, pitch = X.shape
+    for t in (z, kd, X):
+        _require(t.is_cuda and t.shape == X.shape and t.is_contiguous() and t.dtype == X.dtype and t.dtype in _SFX,
+                 "diffusion_solve: contiguous [nlev, pitch] CUDA tensors of one dtype")
+    ncol = pitch if ncol is None else ncol
+    fn = f"ekat_b200_diffusion_solve_{_SFX[X.dtype]}"
+    check(fn, getattr(lib(), fn)(z.data_ptr(), kd.data_ptr(), X.data_ptr(), ncol, nlev, pitch, _stream()))
+    return X
+
+
+def diffusion_matrix(z, kd, ncol=None):
+    """The matrix diffusion_solve implies, written out: returns (dl, d, du), each [nlev, pitch]."""
+    nlev, pitch = z.shape
+    for t in (z, kd):
+        _require(t.is_cuda and t.shape == z.shape and t.is_contiguous() and t.dtype == z.dtype and t.dtype in _SFX,
+                 "diffusion_matrix: contiguous [nlev, pitch] CUDA tensors of one dtype")
+    ncol = pitch if ncol is None else ncol
+    A = torch.empty((3, nlev, pitch), dtype=z.dtype, device=z.device)
+    fn = f"ekat_b200_diffusion_matrix_{_SFX[z.dtype]}"
+    check(fn, getattr(lib(), fn)(z.data_ptr(), kd.data_ptr(), A[0].data_ptr(), A[1].data_ptr(), A[2].data_ptr(), ncol, nlev,
+                                 pitch, _stream()))
+    return A[0], A[1], A[2]

@@ -218,6 +218,91 @@ int ekat_b200_adj_diff_f32(const float* in, float* out, int64_t ncol, int n, int
                            ekat_b200_layout layout, int forward, ekat_b200_stream_t stream);
 
 /* ------------------------------------------------------------------------
+ * ekat::shift_right / ekat::shift_left along every column (SURVEY.md section
+ * 8f-3; reference src/pack/ekat_pack.hpp:521-555: applied pack after pack over
+ * a scalarized column, the ScalarType overloads supplying the end value):
+ *   out[k] = (0 <= k - shift_by < n) ? in[k - shift_by] : fill
+ * shift_by = +1 is shift_right, -1 shift_left; any |shift_by| is accepted.
+ * in != out. Layouts as for adj_diff.
+ *
+ * ekat::index_and_shift<Shift> for every index of every column (reference
+ * src/pack/ekat_pack_kokkos.hpp:71-98): m indices idx per column into the n
+ * scalars of a,
+ *   out[j] = a[idx[j]],  out_shift[j] = a[idx[j] + shift_by].
+ * Where idx[j] or idx[j] + shift_by lies outside [0, n): out[j] is left as the
+ * caller had it and out_shift[j] = quiet NaN -- the reference's debug-build
+ * behaviour (:85-93; its release build reads out of bounds).
+ *   COL_MAJOR: a[c*pitch_a + k], idx[c*pitch_idx + j], out*[c*pitch_out + j];
+ *   LEV_MAJOR: a[k*pitch_a + c], idx[j*pitch_idx + c], out*[j*pitch_out + c].
+ * ---------------------------------------------------------------------- */
+int ekat_b200_shift_f64(const double* in, double* out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out,
+                        ekat_b200_layout layout, int shift_by, double fill, ekat_b200_stream_t stream);
+int ekat_b200_shift_f32(const float* in, float* out, int64_t ncol, int n, int64_t pitch_in, int64_t pitch_out,
+                        ekat_b200_layout layout, int shift_by, float fill, ekat_b200_stream_t stream);
+int ekat_b200_index_and_shift_f64(const double* a, const int* idx, double* out, double* out_shift, int64_t ncol,
+                                  int n, int m, int64_t pitch_a, int64_t pitch_idx, int64_t pitch_out,
+                                  ekat_b200_layout layout, int shift_by, ekat_b200_stream_t stream);
+int ekat_b200_index_and_shift_f32(const float* a, const int* idx, float* out, float* out_shift, int64_t ncol, int n,
+                                  int m, int64_t pitch_a, int64_t pitch_idx, int64_t pitch_out,
+                                  ekat_b200_layout layout, int shift_by, ekat_b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Fused "difference -> (dl, d, du) -> solve" (SURVEY.md section 8f-3): the
+ * finite-difference step that column physics runs right before a tridiagonal
+ * fill -- ekat::adj_diff<Forward> of the level coordinate (reference
+ * src/pack/ekat_pack_kokkos.hpp:139-152) -- the caller's coefficient formula
+ * and the Thomas solve in ONE kernel, so that the three diagonals are never
+ * written to or read from HBM: 4 words per column-level cross HBM (z, kd, X
+ * in, X out) instead of 10 (adj_diff + fill: read 2, write 3; solve: read 4,
+ * write 1). The stencil is the implicit vertical-diffusion step (SHOC-style):
+ *   w[i]  = kd[i] / (z[i+1] - z[i])        i < nlev-1;   w[-1] = w[nlev-1] = 0
+ *   dl[i] = -w[i-1],  du[i] = -w[i],  d[i] = (1 + w[i]) + w[i-1]
+ *   X <- A^-1 X                            (thomas arithmetic, tolerance level)
+ * z, kd, X: [nlev][pitch] level-major (kd[i] = dt * diffusivity at the
+ * interface between levels i and i+1; kd[nlev-1] is not used). The diagonals
+ * are formed with separately rounded IEEE operations, so the implied matrix is
+ * bit-defined: ekat_b200_diffusion_matrix_* writes exactly that matrix (the
+ * two-pass form, and what a caller needs if it wants the matrix itself).
+ * diffusion_solve needs 16-byte aligned operands and pitch and 3 planes of
+ * nlev x 32 columns on chip (nlev <= 300 in double): EKAT_B200_ERR_UNSUPPORTED
+ * otherwise -- use ekat_b200_diffusion_matrix_* + ekat_b200_tridiag_thomas_*.
+ * ---------------------------------------------------------------------- */
+int ekat_b200_diffusion_solve_f64(const double* z, const double* kd, double* X, int64_t ncol, int nlev,
+                                  int64_t pitch, ekat_b200_stream_t stream);
+int ekat_b200_diffusion_solve_f32(const float* z, const float* kd, float* X, int64_t ncol, int nlev, int64_t pitch,
+                                  ekat_b200_stream_t stream);
+int ekat_b200_diffusion_matrix_f64(const double* z, const double* kd, double* dl, double* d, double* du,
+                                   int64_t ncol, int nlev, int64_t pitch, ekat_b200_stream_t stream);
+int ekat_b200_diffusion_matrix_f32(const float* z, const float* kd, float* dl, float* d, float* du, int64_t ncol,
+                                   int nlev, int64_t pitch, ekat_b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Rank-3 layout marshalling: ekat::transpose<c2f|f2c>
+ * for [ni][nk][nj] arrays (reference src/kokkos/ekat_math_utils.hpp:124-147),
+ * on the device, with pitches:
+ *   C side       element (i,k,j) at c[i*c_stride + k*nj + j]      (c_stride >= nk*nj)
+ *   Fortran side element (i,k,j) at f[(j*nk + k)*f_pitch + i]     (f_pitch  >= ni)
+ * c2f != 0: src is the C side, dst the Fortran side; c2f == 0: the reverse.
+ * With (i,k,j) = (column, level, rhs) the C side is the reference's batch
+ * X[col][lev][rhs] (tests/algorithm/tridiag_tests_performance.cpp:181-185) and
+ * the Fortran side the native X[rhs][lev][col]; nj == 1 is the rank-2 case.
+ *
+ * ekat_b200_repack: the row repacking of host_to_device / device_to_host
+ * (reference src/pack/ekat_pack_kokkos.hpp:332-1035): [nrows][n] scalars with
+ * row stride src_stride -> rows of dst_pitch >= n scalars (= npack*N for a
+ * view of Pack<T,N>); zero_pad != 0 also writes zeros into the padding lanes,
+ * as a freshly allocated Kokkos view has them.
+ * ---------------------------------------------------------------------- */
+int ekat_b200_transpose3_f64(const double* src, double* dst, int64_t ni, int nk, int nj, int64_t c_stride,
+                             int64_t f_pitch, int c2f, ekat_b200_stream_t stream);
+int ekat_b200_transpose3_f32(const float* src, float* dst, int64_t ni, int nk, int nj, int64_t c_stride,
+                             int64_t f_pitch, int c2f, ekat_b200_stream_t stream);
+int ekat_b200_repack_f64(const double* src, double* dst, int64_t nrows, int n, int64_t src_stride, int64_t dst_pitch,
+                         int zero_pad, ekat_b200_stream_t stream);
+int ekat_b200_repack_f32(const float* src, float* dst, int64_t nrows, int n, int64_t src_stride, int64_t dst_pitch,
+                         int zero_pad, ekat_b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
  * Verification reductions for the column-sharded multi-GPU driver (SURVEY.md
  * section 8e). Results are DEVICE scalars so they can go straight into one
  * NCCL all-reduce (ekat::Comm::all_reduce, src/core/ekat_comm.hpp:152-162).

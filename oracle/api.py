@@ -180,6 +180,61 @@ class CpuOracle:
         return out
 
 
+    def shift(self, x, shift_by, fill=0.0, packn=1):
+        """ekat::shift_right (shift_by=+1) / shift_left (-1) pack after pack along every column of x [ncol, pitch]."""
+        x = np.ascontiguousarray(x)
+        ncol, pitch = x.shape
+        out = np.zeros_like(x)
+        s = _sfx(x.dtype)
+        cf = ctypes.c_double if x.dtype == np.float64 else ctypes.c_float
+        if self.kind == "port":
+            rc = getattr(self.lib, "ekat_oracle_shift_" + s)(_p(x), _p(out), _i64(ncol), _int(pitch), _i64(pitch),
+                                                             _int(shift_by), cf(fill))
+        else:
+            if shift_by not in (1, -1):
+                raise ValueError("the reference shifts by one place")
+            rc = getattr(self.lib, "ekat_ref_shift_" + s)(_int(max(packn, 1)), _int(shift_by), cf(fill), _p(x), _p(out),
+                                                          _i64(ncol), _i64(pitch))
+        if rc != 0:
+            raise ValueError(f"{self.kind} oracle shift rc={rc}")
+        return out
+
+    def index_and_shift(self, a, idx, shift_by, out0=None, packn=1):
+        """ekat::index_and_shift<shift_by> for every index of every column: a [ncol, n], idx [ncol, m] int32.
+        Returns (index, index_shift); lanes with an out-of-range (shifted) index keep out0 / get NaN."""
+        a = np.ascontiguousarray(a)
+        idx = np.ascontiguousarray(idx, dtype=np.int32)
+        ncol, n = a.shape
+        m = idx.shape[1]
+        out = np.full((ncol, m), -777.0, a.dtype) if out0 is None else np.ascontiguousarray(out0).copy()
+        outs = np.zeros((ncol, m), a.dtype)
+        s = _sfx(a.dtype)
+        if self.kind == "port":
+            rc = getattr(self.lib, "ekat_oracle_index_and_shift_" + s)(_p(a), _p(idx), _p(out), _p(outs), _i64(ncol), _int(n),
+                                                                       _int(m), _i64(n), _int(shift_by))
+        else:
+            rc = getattr(self.lib, "ekat_ref_index_and_shift_" + s)(_int(packn), _int(shift_by), _p(a), _p(idx), _p(out),
+                                                                    _p(outs), _i64(ncol), _int(n), _int(m))
+        if rc != 0:
+            raise ValueError(f"{self.kind} oracle index_and_shift rc={rc}")
+        return out, outs
+
+    def transpose(self, sv, shape, c2f):
+        """ekat::transpose<c2f|f2c> of a flat array: shape = (ni, nk) or (ni, nk, nj). Returns the flat result."""
+        sv = np.ascontiguousarray(sv).ravel()
+        dv = np.zeros_like(sv)
+        ni, nk = shape[0], shape[1]
+        nj = shape[2] if len(shape) == 3 else 0
+        s = _sfx(sv.dtype)
+        if self.kind == "port":
+            rc = getattr(self.lib, "ekat_oracle_transpose_" + s)(_p(sv), _p(dv), _int(ni), _int(nk), _int(max(nj, 1)), _int(1 if c2f else 0))
+        else:
+            rc = getattr(self.lib, "ekat_ref_transpose_" + s)(_p(sv), _p(dv), _int(ni), _int(nk), _int(nj), _int(1 if c2f else 0))
+        if rc != 0:
+            raise ValueError(f"{self.kind} oracle transpose rc={rc}")
+        return dv
+
+
 _cache = {}
 
 

@@ -8,6 +8,9 @@
 //   ekat::tridiag::{thomas,cr,bfb}       (src/algorithm/ekat_tridiag.hpp:323-678)
 //   ekat::LinInterp::{setup,lin_interp}  (src/algorithm/ekat_lin_interp.hpp:69-126)
 //   ekat::adj_diff<Forward>              (src/pack/ekat_pack_kokkos.hpp:100-164)
+//   ekat::shift_left / shift_right       (src/pack/ekat_pack.hpp:521-555)
+//   ekat::index_and_shift<Shift>         (src/pack/ekat_pack_kokkos.hpp:71-98)
+//   ekat::transpose<c2f|f2c> (rank 2, 3) (src/kokkos/ekat_math_utils.hpp:90-147)
 //   ekat::impl::view_reduction<Serialize> (src/algorithm/ekat_reduction_utils.hpp:67-144)
 //   ekat::test::fill_tridiag_matrix / fill_data_matrix / matvec
 //                                        (tests/algorithm/tridiag_tests.hpp:11-88)
@@ -40,6 +43,8 @@
 #undef private
 #include "ekat_tridiag.hpp"
 #include "ekat_reduction_utils.hpp"
+#include "ekat_math_utils.hpp"
+#include "ekat_pack_kokkos.hpp"
 #include "tridiag_tests.hpp"
 
 namespace {
@@ -256,6 +261,80 @@ int adj_diff(int packn, int forward, const S* in, S* out, int64_t ncol, int64_t 
 #undef EKAT_REF_AD
 }
 
+// ekat::shift_right / shift_left pack after pack along a scalarized column (src/pack/ekat_pack.hpp:521-555), the way
+// adj_diff chains them (ekat_pack_kokkos.hpp:118-126): the neighbouring pack supplies the incoming lane, the scalar
+// `fill` at the end of the column. dir = +1: shift_right, -1: shift_left. in, out: [ncol][pitch], pitch % N == 0.
+template <class S, int N>
+int shift_n(int dir, S fill, const S* in, S* out, int64_t ncol, int64_t pitch) {
+  using P = ekat::Pack<S, N>;
+  if (pitch % N) return -3;
+  const int np = (int)(pitch / N);
+  Kokkos::parallel_for(Policy((int)ncol, 1), [&](const Member& team) {
+    const int c = team.league_rank();
+    const P* v = reinterpret_cast<const P*>(in + (size_t)c * pitch);
+    P* o = reinterpret_cast<P*>(out + (size_t)c * pitch);
+    for (int k = 0; k < np; ++k) {
+      if (dir > 0) o[k] = k > 0 ? ekat::shift_right(v[k - 1], v[k]) : ekat::shift_right(fill, v[k]);
+      else o[k] = k < np - 1 ? ekat::shift_left(v[k + 1], v[k]) : ekat::shift_left(fill, v[k]);
+    }
+  });
+  return 0;
+}
+template <class S>
+int shift(int packn, int dir, S fill, const S* in, S* out, int64_t ncol, int64_t pitch) {
+  switch (packn) {
+    case 1: return shift_n<S, 1>(dir, fill, in, out, ncol, pitch);
+    case 2: return shift_n<S, 2>(dir, fill, in, out, ncol, pitch);
+    case 4: return shift_n<S, 4>(dir, fill, in, out, ncol, pitch);
+    case 8: return shift_n<S, 8>(dir, fill, in, out, ncol, pitch);
+    case 16: return shift_n<S, 16>(dir, fill, in, out, ncol, pitch);
+    default: return -4;
+  }
+}
+
+// ekat::index_and_shift<Shift>(a, idx_pack, index, index_shift) (src/pack/ekat_pack_kokkos.hpp:71-98) for every index
+// pack of every column: a [ncol][n] scalars, idx [ncol][m] ints (m % N == 0), out / out_shift [ncol][m]. This library
+// is built without NDEBUG, so out-of-range lanes behave as the header's debug branch says: `index` keeps what the
+// caller put there, `index_shift` is ekat::invalid.
+template <class S, int N, int SH>
+int index_and_shift_n(const S* a, const int* idx, S* out, S* out_shift, int64_t ncol, int n, int m) {
+  using P = ekat::Pack<S, N>;
+  using IP = ekat::Pack<int, N>;
+  if (m % N) return -3;
+  Kokkos::parallel_for(Policy((int)ncol, 1), [&](const Member& team) {
+    const int c = team.league_rank();
+    V1<const S> row(a + (size_t)c * n, n);
+    for (int j = 0; j < m / N; ++j) {
+      IP ip;
+      P p0, p1;
+      for (int l = 0; l < N; ++l) {
+        ip[l] = idx[(size_t)c * m + j * N + l];
+        p0[l] = out[(size_t)c * m + j * N + l];
+        p1[l] = out_shift[(size_t)c * m + j * N + l];
+      }
+      ekat::index_and_shift<SH>(row, ip, p0, p1);
+      for (int l = 0; l < N; ++l) {
+        out[(size_t)c * m + j * N + l] = p0[l];
+        out_shift[(size_t)c * m + j * N + l] = p1[l];
+      }
+    }
+  });
+  return 0;
+}
+template <class S>
+int index_and_shift(int packn, int sh, const S* a, const int* idx, S* out, S* out_shift, int64_t ncol, int n, int m) {
+#define EKAT_REF_IS(N_)                                                                                      \
+  case N_:                                                                                                   \
+    return sh == 1 ? index_and_shift_n<S, N_, 1>(a, idx, out, out_shift, ncol, n, m)                          \
+                   : sh == -1 ? index_and_shift_n<S, N_, -1>(a, idx, out, out_shift, ncol, n, m)              \
+                              : sh == 2 ? index_and_shift_n<S, N_, 2>(a, idx, out, out_shift, ncol, n, m) : -5;
+  switch (packn) {
+    EKAT_REF_IS(1) EKAT_REF_IS(4) EKAT_REF_IS(16)
+    default: return -4;
+  }
+#undef EKAT_REF_IS
+}
+
 template <class S>
 int view_reduction(int packn, int serialize, const S* in, S* out, int64_t ncol, int begin, int end, int64_t pitch) {
 #define EKAT_REF_VR(N_) \
@@ -271,6 +350,33 @@ int view_reduction(int packn, int serialize, const S* in, S* out, int64_t ncol, 
 }  // namespace
 
 extern "C" {
+int ekat_ref_shift_f64(int packn, int dir, double fill, const double* in, double* out, int64_t ncol, int64_t pitch) {
+  return shift<double>(packn, dir, fill, in, out, ncol, pitch);
+}
+int ekat_ref_shift_f32(int packn, int dir, float fill, const float* in, float* out, int64_t ncol, int64_t pitch) {
+  return shift<float>(packn, dir, fill, in, out, ncol, pitch);
+}
+int ekat_ref_index_and_shift_f64(int packn, int sh, const double* a, const int* idx, double* out, double* out_shift,
+                                 int64_t ncol, int n, int m) {
+  return index_and_shift<double>(packn, sh, a, idx, out, out_shift, ncol, n, m);
+}
+int ekat_ref_index_and_shift_f32(int packn, int sh, const float* a, const int* idx, float* out, float* out_shift,
+                                 int64_t ncol, int n, int m) {
+  return index_and_shift<float>(packn, sh, a, idx, out, out_shift, ncol, n, m);
+}
+// ekat::transpose (src/kokkos/ekat_math_utils.hpp:90-147): c2f != 0 -> TransposeDirection::c2f; nj == 0 -> the rank-2 form
+int ekat_ref_transpose_f64(const double* sv, double* dv, int ni, int nk, int nj, int c2f) {
+  const auto dir = c2f ? ekat::TransposeDirection::c2f : ekat::TransposeDirection::f2c;
+  if (nj == 0) ekat::transpose(sv, dv, ni, nk, dir);
+  else ekat::transpose(sv, dv, ni, nk, nj, dir);
+  return 0;
+}
+int ekat_ref_transpose_f32(const float* sv, float* dv, int ni, int nk, int nj, int c2f) {
+  const auto dir = c2f ? ekat::TransposeDirection::c2f : ekat::TransposeDirection::f2c;
+  if (nj == 0) ekat::transpose(sv, dv, ni, nk, dir);
+  else ekat::transpose(sv, dv, ni, nk, nj, dir);
+  return 0;
+}
 int ekat_ref_adj_diff_f64(int packn, int forward, const double* in, double* out, int64_t ncol, int64_t pitch) {
   return adj_diff<double>(packn, forward, in, out, ncol, pitch);
 }

@@ -8,6 +8,7 @@
 #include <Kokkos_Core.hpp>  // the stand-in: only its View type is used
 
 #include "ekat_b200/ekat_lin_interp.hpp"
+#include "ekat_b200/ekat_pack_kokkos.hpp"
 #include "ekat_b200/ekat_reduction_utils.hpp"
 #include "ekat_b200/ekat_tridiag.hpp"
 
@@ -110,6 +111,26 @@ int main(int argc, char** argv) {
     bad += !throws_invalid([&] { ekat::b200::adj_diff<true>(nullptr, d8, o7); });     // extents differ
     bad += !throws_invalid([&] { ekat::b200::adj_diff<true>(nullptr, d8, alias); });  // in == out
     (void)o8;
+  }
+  // shift_left / shift_right / index_and_shift / transpose: empty batches, extents, aliasing
+  {
+    VR2<const double> d0(fake, 0, 128), d8(fake, 8, 128);
+    VR2<double> o0(fake, 0, 128), o7(fake + 4096, 8, 127), alias(fake, 8, 128);
+    ekat::b200::shift_right(nullptr, 0.0, d0, o0);
+    ekat::b200::shift_left(nullptr, 1.5, d0, o0);
+    VR2<const Pack16> p0(reinterpret_cast<const Pack16*>(fake), 0, 8);
+    VR2<Pack16> q0(reinterpret_cast<Pack16*>(fake), 0, 8);
+    ekat::b200::shift_right(nullptr, 0.0, p0, q0);
+    bad += !throws_invalid([&] { ekat::b200::shift_left(nullptr, 0.0, d8, o7); });
+    bad += !throws_invalid([&] { ekat::b200::shift_right(nullptr, 0.0, d8, alias); });
+    using VI2 = Kokkos::View<int**, Kokkos::LayoutRight, Kokkos::MemoryUnmanaged>;
+    VI2 i0(reinterpret_cast<int*>(fake), 0, 128), i8(reinterpret_cast<int*>(fake), 8, 64);
+    ekat::b200::index_and_shift<1>(nullptr, d0, i0, o0, o0);
+    VR2<double> o8(fake + 4096, 8, 128);
+    bad += !throws_invalid([&] { ekat::b200::index_and_shift<1>(nullptr, d8, i8, o8, o8); });  // m differs from the outputs
+    ekat::b200::transpose<ekat::b200::TransposeDirection::c2f>(nullptr, fake, fake + 64, 0, 72, 10);
+    ekat::b200::transpose<ekat::b200::TransposeDirection::f2c>(nullptr, fakef, fakef + 64, 0, 72);
+    bad += !throws_invalid([&] { ekat::b200::transpose<ekat::b200::TransposeDirection::c2f>(nullptr, fake, fake + 64, -1, 72, 10); });
   }
   if (bad) {
     std::printf("adapter argument checks FAILED (%d)\n", bad);
