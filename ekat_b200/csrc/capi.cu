@@ -22,6 +22,8 @@ int tridiag_tma_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev,
 template <typename R>
 int tridiag_cr_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride, cudaStream_t stream);
 template <typename R>
+int tridiag_cr_blk(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride, cudaStream_t stream);
+template <typename R>
 int tridiag_tma_shared_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride,
                           cudaStream_t stream);
 template <typename R>
@@ -140,7 +142,13 @@ static int tridiag_entry(int solver, R* dl, R* d, R* du, R* X, int64_t ncol, int
   }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (solver == SOLVER_CR) {
-    if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && nA == 1 && nrhs == 1 && !flags && tuning().variant == kVarAuto) {
+    const int var = tuning().variant;
+    if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && nA == 1 && nrhs == 1 && !flags && var == kVarAuto) {
+      // many columns of <= 128 levels: two levels per barrier in registers, persistent double-buffered CTAs (tridiag_cr_blk.cu)
+      const int rc = tridiag_cr_blk<R>(dl, d, du, X, ncol, nlev, a_stride, x_stride, st);
+      if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+    }
+    if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && nA == 1 && nrhs == 1 && !flags && (var == kVarAuto || var == kVarCrPerLevel)) {
       const int rc = tridiag_cr_tma<R>(dl, d, du, X, ncol, nlev, a_stride, x_stride, st);  // many columns (tridiag_cr_tma.cu)
       if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
     }
