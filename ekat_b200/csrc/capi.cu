@@ -22,8 +22,6 @@ int tridiag_tma_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev,
 template <typename R>
 int tridiag_cr_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride, cudaStream_t stream);
 template <typename R>
-int tridiag_cr_blk(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride, cudaStream_t stream);
-template <typename R>
 int tridiag_tma_shared_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride,
                           cudaStream_t stream);
 template <typename R>
@@ -143,11 +141,6 @@ static int tridiag_entry(int solver, R* dl, R* d, R* du, R* X, int64_t ncol, int
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (solver == SOLVER_CR) {
     const int var = tuning().variant;
-    if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && nA == 1 && nrhs == 1 && !flags && var == kVarAuto) {
-      // many columns of <= 128 levels: two levels per barrier in registers, persistent double-buffered CTAs (tridiag_cr_blk.cu)
-      const int rc = tridiag_cr_blk<R>(dl, d, du, X, ncol, nlev, a_stride, x_stride, st);
-      if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
-    }
     if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && nA == 1 && nrhs == 1 && !flags && (var == kVarAuto || var == kVarCrPerLevel)) {
       const int rc = tridiag_cr_tma<R>(dl, d, du, X, ncol, nlev, a_stride, x_stride, st);  // many columns (tridiag_cr_tma.cu)
       if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
@@ -389,7 +382,8 @@ int ekat_b200_device_alloc(void** ptr, size_t bytes) {
 int ekat_b200_device_free(void* ptr) { return ptr ? check_cuda(cudaFree(ptr)) : EKAT_B200_OK; }
 
 int ekat_b200_debug_trace(int64_t* out, int n) {
-  return (out && n > 0) ? debug_trace(reinterpret_cast<long long*>(out), n) : EKAT_B200_ERR_INVALID;
+  if (!out || n <= 0) return EKAT_B200_ERR_INVALID;
+  return debug_trace(reinterpret_cast<long long*>(out), n);
 }
 
 int ekat_b200_version(void) { return EKAT_B200_VERSION; }

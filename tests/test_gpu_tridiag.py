@@ -291,9 +291,7 @@ def test_shared_matrix_persistent_many_items(cuda, port, dt, solver):
 @pytest.mark.parametrize("dt", ["f64", "f32"])
 def test_cr_many_columns_bit_exact(cuda, port, dt):
     """Cyclic reduction at column counts that take the TMA kernels: bit-identical to the reference's CR for
-    power-of-two, odd and tiny level counts, ragged last tile. Default route: the blocked kernel (tridiag_cr_blk.cu,
-    two levels per barrier in registers) up to 128 levels, the level-per-barrier kernel (tridiag_cr_tma.cu) above;
-    tuning variant 14 pins the latter everywhere."""
+    power-of-two, odd and tiny level counts, ragged last tile (tridiag_cr_tma.cu; tuning variant 14 pins it too)."""
     npdt, _ = DT[dt]
     from ekat_b200._lib import lib
     cases = [(128, 9472 + 5), (72, 9600), (43, 9473), (129, 9480), (5, 9999), (2, 9500), (1, 9476), (3, 9481), (65, 9700)]
@@ -305,7 +303,7 @@ def test_cr_many_columns_bit_exact(cuda, port, dt):
                 want = port.tridiag("cr", A.copy(), B.copy())
                 got, Aout = run_gpu("cr", A, B, ekat_b200.LEV_MAJOR, cuda, pad=(-ncol) % 4)
                 name = lib().ekat_b200_last_kernel().decode()
-                assert name.startswith("tridiag_cr_blk" if variant == 0 and nrow <= 128 else "tridiag_cr_tma"), name
+                assert name.startswith("tridiag_cr_tma"), name
                 assert bits_equal(got, want), (dt, variant, nrow, ncol, rel_diff(want, got))
                 assert bits_equal(Aout, A)
         finally:
@@ -313,29 +311,23 @@ def test_cr_many_columns_bit_exact(cuda, port, dt):
 
 
 @pytest.mark.parametrize("dt", ["f64", "f32"])
-def test_cr_blocked_every_level_count(cuda, port, dt):
-    """tridiag_cr_blk.cu at every level count 1..128 (every combination of leading single level, number of two-level
-    stages, missing right neighbours in the last block, 1x1 / 2x2 bottom solve), a ragged last tile, more tiles than
-    CTAs (both tile buffers reused), and strongly dominant matrices whose reduced off-diagonals leave the range of
-    the speculative division (the full-range repeat of a block)."""
+def test_cr_every_level_count(cuda, port, dt):
+    """tridiag_cr_tma.cu at every level count 1..128 (every number of levels of the reduction, missing right
+    neighbours, 1x1 / 2x2 bottom solve), ragged last tiles, and strongly dominant matrices whose reduced
+    off-diagonals underflow towards zero within a few levels."""
     npdt, _ = DT[dt]
     from ekat_b200._lib import lib
     for nrow in range(1, 129):
-        ncol = 4736 + 16 * (nrow % 3) + nrow % 7
+        ncol = 9472 + 16 * (nrow % 3) + nrow % 7
         A, B = port.fill_tridiag(npdt, ncol, nrow, 1, 1, col0=nrow)
-        if nrow % 5 == 0:  # off-diagonals 1e-3 of the diagonal: dl, du underflow past 2^-120 within a few levels
+        if nrow % 5 == 0:  # off-diagonals 1e-3 of the diagonal
             A[:, 0] *= 1e-3
             A[:, 2] *= 1e-3
         want = port.tridiag("cr", A.copy(), B.copy())
         got, Aout = run_gpu("cr", A, B, ekat_b200.LEV_MAJOR, cuda, pad=(-ncol) % 4)
-        assert lib().ekat_b200_last_kernel().decode().startswith("tridiag_cr_blk"), lib().ekat_b200_last_kernel()
+        assert lib().ekat_b200_last_kernel().decode().startswith("tridiag_cr_tma"), lib().ekat_b200_last_kernel()
         assert bits_equal(got, want), (dt, nrow, ncol, rel_diff(want, got))
         assert bits_equal(Aout, A)
-    ncol, nrow = 148 * 16 * 5 + 9, 128  # five tiles per CTA and a ragged one
-    A, B = port.fill_tridiag(npdt, ncol, nrow, 1, 1, col0=7)
-    want = port.tridiag("cr", A.copy(), B.copy())
-    got, _ = run_gpu("cr", A, B, ekat_b200.LEV_MAJOR, cuda, pad=(-ncol) % 4)
-    assert bits_equal(got, want)
 
 
 @pytest.mark.parametrize("dt", ["f64", "f32"])
