@@ -20,6 +20,9 @@ template <typename R>
 int tridiag_tma_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride,
                    cudaStream_t stream);
 template <typename R>
+int tridiag_cm_rhs(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nA, int nrhs, int64_t a_stride,
+                   int64_t x_stride, unsigned flags, cudaStream_t stream);
+template <typename R>
 int tridiag_cr_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride, cudaStream_t stream);
 template <typename R>
 int tridiag_tma_shared_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride,
@@ -156,6 +159,12 @@ static int tridiag_entry(int solver, R* dl, R* d, R* du, R* X, int64_t ncol, int
       if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
     }
     const int rc = tridiag_tma_cm<R>(solver == SOLVER_BFB, dl, d, du, X, ncol, nlev, a_stride, x_stride, st);
+    if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+  }
+  if (layout == EKAT_B200_LAYOUT_COL_MAJOR && (nrhs > 1 || flags) && tuning().variant == kVarAuto) {
+    // reference layout, several right-hand sides (or the in-place side effect): bulk-copied column tiles, one thread
+    // per (column, right-hand side) (tridiag_cm_rhs.cu)
+    const int rc = tridiag_cm_rhs<R>(solver == SOLVER_BFB, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, flags, st);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }
   return tridiag_tile<R>(solver == SOLVER_BFB ? 1 : 0, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, layout,

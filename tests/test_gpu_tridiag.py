@@ -362,3 +362,45 @@ def test_small_batch_kernel_two_sided_elimination(cuda, port, dt):
     A2[:, 2, -1, :] = np.nan
     got2, _ = run_gpu("thomas", A2, B, ekat_b200.LEV_MAJOR, cuda)
     assert bits_equal(got2, got)
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+def test_reference_layout_many_rhs(cuda, port, dt):
+    """tridiag_cm_rhs.cu: the reference layout A[col][3][lev][nA], X[col][lev][nrhs] with several right-hand sides
+    (BASELINE config 4 as a reference caller holds it; the reference perf driver's default 128 x 43,
+    tests/algorithm/tridiag_tests_performance.cpp:33-37), one matrix per column and one per right-hand side, ragged
+    last tiles, tile widths forced through the tuning knob, and the in-place side effects -- bfb bit for bit, thomas to
+    the tolerance, dl / d as the reference leaves them."""
+    from ekat_b200._lib import lib
+    npdt, _ = DT[dt]
+    cases = [(128, 10, 1, 601), (128, 10, 10, 77), (72, 4, 1, 1000), (72, 4, 4, 333), (128, 43, 1, 70), (16, 2, 1, 4999),
+             (8, 32, 1, 130), (100, 6, 6, 41), (2, 2, 1, 50), (4, 1, 1, 300)]
+    for nrow, nrhs, nA, ncol in cases:
+        A, B = port.fill_tridiag(npdt, ncol, nrow, nA, nrhs, col0=5)
+        for solver in ("bfb", "thomas"):
+            want = port.tridiag(solver, A.copy(), B.copy())
+            for clobber in (False, True):
+                if nrhs == 1 and not clobber:
+                    continue  # one right-hand side without side effects belongs to the TMA tensor kernels
+                for cols in (0, 1, 3):
+                    try:
+                        lib().ekat_b200_set_tuning(cols, 0, 0)
+                        got, Aout = run_gpu(solver, A, B, ekat_b200.COL_MAJOR, cuda, clobber=clobber)
+                    finally:
+                        lib().ekat_b200_set_tuning(0, 0, 0)
+                    name = lib().ekat_b200_last_kernel().decode()
+                    row_bytes = nrow * nA * np.dtype(npdt).itemsize, nrow * nrhs * np.dtype(npdt).itemsize
+                    if all(b % 16 == 0 for b in row_bytes):  # bulk copies move multiples of 16 bytes; other rows take the tile kernel
+                        assert name.startswith("tridiag_cm_rhs"), (name, nrow, nrhs, nA)
+                    check(solver, got, want, npdt, (dt, nrow, nrhs, nA, ncol, clobber))
+                    if not clobber:
+                        assert bits_equal(Aout, A)
+                    else:
+                        # what the reference's in-place solvers leave: bfb multipliers in dl(1..) and pivots in d
+                        # (:292-303), serial thomas pivots in d only (:216-227); du never changes
+                        Aref = A.copy()
+                        port.tridiag("bfb", Aref, B.copy())
+                        assert bits_equal(Aout[:, 2], A[:, 2])
+                        assert bits_equal(Aout[:, 1], Aref[:, 1])
+                        assert bits_equal(Aout[:, 0, 1:], Aref[:, 0, 1:] if solver == "bfb" else A[:, 0, 1:])
+                        assert bits_equal(Aout[:, 0, 0], A[:, 0, 0])  # dl(0) is never touched

@@ -52,6 +52,12 @@ for c in cases:
         for _ in range(REPS):
             X.copy_(B)
             getattr(T, c.split("_")[1])(dl, d, du, X, layout=ekat_b200.COL_MAJOR)
+    elif c in ("cm10_thomas", "cm10_bfb"):  # reference layout X[col][lev][10], one matrix per column
+        dl, d, du, B = T.fill(dt, NCOL, NLEV, 1, 10, layout=ekat_b200.COL_MAJOR, device=dev)
+        X = B.clone()
+        for _ in range(REPS):
+            X.copy_(B)
+            getattr(T, c.split("_")[1])(dl, d, du, X, layout=ekat_b200.COL_MAJOR)
     elif c == "li72":
         x1, y1, x2 = li_fill(dt, NCOL, 72, 128, 16, device=dev)
         li = LinInterp(NCOL, 72, 128, dt, 16, device=dev)
