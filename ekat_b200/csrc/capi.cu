@@ -23,6 +23,9 @@ template <typename R>
 int tridiag_cm_rhs(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nA, int nrhs, int64_t a_stride,
                    int64_t x_stride, unsigned flags, cudaStream_t stream);
 template <typename R>
+int tridiag_cr_warp(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nrhs, int64_t a_stride, int64_t x_stride, int layout,
+                    cudaStream_t stream);
+template <typename R>
 int tridiag_cr_tma(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride, cudaStream_t stream);
 template <typename R>
 int tridiag_tma_shared_cm(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int64_t a_stride, int64_t x_stride,
@@ -146,6 +149,12 @@ static int tridiag_entry(int solver, R* dl, R* d, R* du, R* X, int64_t ncol, int
     const int var = tuning().variant;
     if (layout == EKAT_B200_LAYOUT_LEV_MAJOR && nA == 1 && nrhs == 1 && !flags && (var == kVarAuto || var == kVarCrPerLevel)) {
       const int rc = tridiag_cr_tma<R>(dl, d, du, X, ncol, nlev, a_stride, x_stride, st);  // many columns (tridiag_cr_tma.cu)
+      if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+    }
+    if (nA == 1 && !flags && var == kVarAuto) {
+      // few columns, the reference layout, several right-hand sides: a warp per (column, rhs group), rows in registers,
+      // neighbours by shuffle (tridiag_cr_warp.cu)
+      const int rc = tridiag_cr_warp<R>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, layout, st);
       if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
     }
     return tridiag_tile<R>(2, dl, d, du, X, ncol, nlev, nA, nrhs, a_stride, x_stride, layout, flags, st);
