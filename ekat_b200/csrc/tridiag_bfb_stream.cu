@@ -27,11 +27,13 @@
 
 namespace ekb {
 
-template <typename R, int CPT, int NS, int LBT, bool CM, bool PP>
+template <typename R, int CPT, int NS, int LBT, bool CM, bool PP, bool CLB>
 __global__ void __launch_bounds__(PP ? 96 : 64)
 k_tridiag_bfb_stream(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
                      const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mx, R* __restrict__ X,
-                     int64_t ncol, int nlev, int64_t x_stride, int pd) {
+                     int64_t ncol, int nlev, int64_t x_stride, int pd, int clob_arg, R* __restrict__ DLg, R* __restrict__ Dg,
+                     int64_t a_stride) {
+  const int clob = CLB ? clob_arg : 0;  // (the instantiation without side effects carries no multiplier registers)
   using V = Vec<R, CPT>;
   constexpr int LB = LBT, W = 32 * CPT, CH = LB * 32;
   constexpr unsigned CHUNK_BYTES = LB * W * sizeof(R);
@@ -53,6 +55,7 @@ k_tridiag_bfb_stream(const __grid_constant__ CUtensorMap mdl, const __grid_const
   V* P0 = reinterpret_cast<V*>(smem_raw + off);  // d -> d'
   V* RG = P0 + (size_t)nch * CH;                 // [NS][3][LB][32]
   V* OB = RG + (size_t)NS * 3 * CH;              // [2][LB][32]
+  V* OBM = OB + 2 * CH;                          // [2][LB][32] multipliers on their way to dl (clob bit 0 only)
 
   const int c0 = blockIdx.x * W;
   const int row0 = blockIdx.y * nlev;
@@ -70,10 +73,9 @@ k_tridiag_bfb_stream(const __grid_constant__ CUtensorMap mdl, const __grid_const
       if (CM) tma_load_2d_hint(dst, m, k * LB, c0, bar, pol);
       else tma_load_2d_hint(dst, m, c0, row0 + k * LB, bar, pol);
     };
-    auto store_chunk = [&](int k, const void* src, uint64_t pol) {
-      if (CM) tma_store_2d_hint(&mx, k * LB, c0, src, pol);
-      else tma_store_2d_hint(&mx, c0, row0 + k * LB, src, pol);
-      tma_store_commit();
+    auto store_chunk = [&](const CUtensorMap* m, int k, const void* src, uint64_t pol) {  // (the caller commits)
+      if (CM) tma_store_2d_hint(m, k * LB, c0, src, pol);
+      else tma_store_2d_hint(m, c0, row0 + k * LB, src, pol);
     };
     auto issue_use = [&](int u) {
       const int s = u % NS;
@@ -115,12 +117,19 @@ k_tridiag_bfb_stream(const __grid_constant__ CUtensorMap mdl, const __grid_const
       mbar_wait(&dbar[b], (dph >> b) & 1u);
       dph ^= 1u << b;
       const bool st = t < nch ? (k <= nch - 3) : (CM || k != nfull);
+      bool any = st;
       if (st) {
-        store_chunk(k, OB + (size_t)b * CH, t < nch ? pol_keep : pol_stream);
+        store_chunk(&mx, k, OB + (size_t)b * CH, t < nch ? pol_keep : pol_stream);
         if (t < nch) ++fwd_stores;
       }
+      if (clob && t < nch && k != nfull) {  // the factorisation goes back too (a ragged top chunk is stored by the sweeping warp)
+        if (clob & 1) store_chunk(&mdl, k, OBM + (size_t)b * CH, pol_stream);
+        if (clob & 2) store_chunk(&md, k, P0 + (size_t)k * CH, pol_stream);
+        any = true;
+      }
+      if (any) tma_store_commit();
       if (pending >= 0) {
-        if (st) tma_store_wait_read<1>();
+        if (any) tma_store_wait_read<1>();
         else tma_store_wait_read<0>();
         mbar_arrive(&obar[pending]);
         pending = -1;
@@ -180,7 +189,7 @@ k_tridiag_bfb_stream(const __grid_constant__ CUtensorMap mdl, const __grid_const
     const V* st = RG + (size_t)s * 3 * CH;
     V* p0 = P0 + (size_t)k * CH;
     V* ob = OB + (size_t)b * CH;
-    V a[LB], bb[LB], c[LB], x[LB], o0[LB], o1[LB];
+    V a[LB], bb[LB], c[LB], x[LB], o0[LB], o1[LB], om[LB];
 #pragma unroll
     for (int u = 0; u < LB; ++u) {
       a[u] = ld(st, u);
@@ -207,7 +216,8 @@ k_tridiag_bfb_stream(const __grid_constant__ CUtensorMap mdl, const __grid_const
       su[j] = uprev[j];
     }
     bool bad = false;
-    bfb_fwd_chunk<R, CPT, LB, false>(a, bb, c, x, o0, o1, dprev, xprev, uprev, k == 0, bad);
+    if constexpr (CLB) bfb_fwd_chunk_m<R, CPT, LB, false>(a, bb, c, x, o0, o1, om, dprev, xprev, uprev, k == 0, bad);
+    else bfb_fwd_chunk<R, CPT, LB, false>(a, bb, c, x, o0, o1, dprev, xprev, uprev, k == 0, bad);
     if (__any_sync(0xffffffffu, bad)) {  // rare operands somewhere in the warp: redo with the full-range division
 #pragma unroll
       for (int j = 0; j < CPT; ++j) {
@@ -215,7 +225,8 @@ k_tridiag_bfb_stream(const __grid_constant__ CUtensorMap mdl, const __grid_const
         xprev[j] = sx[j];
         uprev[j] = su[j];
       }
-      bfb_fwd_chunk<R, CPT, LB, true>(a, bb, c, x, o0, o1, dprev, xprev, uprev, k == 0, bad);
+      if constexpr (CLB) bfb_fwd_chunk_m<R, CPT, LB, true>(a, bb, c, x, o0, o1, om, dprev, xprev, uprev, k == 0, bad);
+      else bfb_fwd_chunk<R, CPT, LB, true>(a, bb, c, x, o0, o1, dprev, xprev, uprev, k == 0, bad);
     }
     if (PP && k < nch - 1) {  // hand the chain on before anything else: the other warp's chunk starts now
       V h0, h1, h2;
@@ -235,8 +246,29 @@ k_tridiag_bfb_stream(const __grid_constant__ CUtensorMap mdl, const __grid_const
     wait_ob(b, k >> 1);
 #pragma unroll
     for (int u = 0; u < LB; ++u) t_st<R, CPT, LB, CM>(ob, u, lane, o1[u]);
+    if (CLB && (clob & 1)) {
+      V* obm = OBM + (size_t)b * CH;
+#pragma unroll
+      for (int u = 0; u < LB; ++u) t_st<R, CPT, LB, CM>(obm, u, lane, om[u]);
+    }
+    if (CLB && clob && !CM && k == nfull) {  // ragged top chunk: a tensor store would spill into the next matrix' rows
+      const int64_t col = (int64_t)c0 + lane * CPT;
+#pragma unroll
+      for (int u = 0; u < LB; ++u) {
+        if (u < ntail) {
+          const size_t g = (size_t)(row0 + k * LB + u) * a_stride + col;
+#pragma unroll
+          for (int j = 0; j < CPT; ++j) {
+            if (col + j < ncol) {
+              if (clob & 1) __stcs(DLg + g + j, om[u].v[j]);
+              if (clob & 2) __stcs(Dg + g + j, o0[u].v[j]);
+            }
+          }
+        }
+      }
+    }
     if (PP && k == nch - 1) hand_over();  // turn-around: the top chunk's d' and x' must be in shared memory first
-    publish(b, k <= nch - 3);             // x' of the last two chunks stays in OB for the way back
+    publish(b, k <= nch - 3 || clob);     // x' of the last two chunks stays in OB for the way back
   }
 
   // ---------------------------------------------------------------- back substitution
@@ -348,9 +380,9 @@ k_tridiag_bfb_stream(const __grid_constant__ CUtensorMap mdl, const __grid_const
 }
 
 // ------------------------------------------------------------------------------------------- host side
-template <typename R, int NS, bool CM, bool PP>
-static int launch_stream(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
-                         int pd, size_t smem, cudaStream_t stream, const char* name) {
+template <typename R, int NS, bool CM, bool PP, bool CLB>
+static int launch_stream_(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
+                         int pd, size_t smem, cudaStream_t stream, const char* name, int clob) {
   constexpr int CPT = TmaCfg<R>::CPT, LB = TmaGeom<R, CM>::LB, W = 32 * CPT;
   CUtensorMap mdl, md, mdu, mx;
   bool ok;
@@ -364,18 +396,26 @@ static int launch_stream(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int n
          make_tensor_map_2d<R>(&mdu, du, ncol, rows, a_stride, W, LB, 0) && make_tensor_map_2d<R>(&mx, X, ncol, rows, x_stride, W, LB, 0);
   }
   if (!ok) return EKAT_B200_ERR_UNSUPPORTED;
-  auto k = k_tridiag_bfb_stream<R, CPT, NS, LB, CM, PP>;
+  auto k = k_tridiag_bfb_stream<R, CPT, NS, LB, CM, PP, CLB>;
   int rc = allow_smem(k, smem);
   if (rc) return rc;
   dim3 grid((unsigned)((ncol + W - 1) / W), (unsigned)nmat);
-  k<<<grid, PP ? 96 : 64, smem, stream>>>(mdl, md, mdu, mx, X, ncol, nlev, x_stride, pd);
+  k<<<grid, PP ? 96 : 64, smem, stream>>>(mdl, md, mdu, mx, X, ncol, nlev, x_stride, pd, clob, dl, d, a_stride);
   note_launch(name);
   return check_cuda(cudaGetLastError());
 }
 
+template <typename R, int NS, bool CM, bool PP>
+static int launch_stream(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
+                         int pd, size_t smem, cudaStream_t stream, const char* name, int clob) {
+  if (!CM && clob) return launch_stream_<R, NS, CM, PP, true>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name, clob);
+  return launch_stream_<R, NS, CM, PP, false>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem, stream, name, 0);
+}
+
 template <typename R, bool CM>
 int tridiag_bfb_stream(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
-                       cudaStream_t stream) {
+                       cudaStream_t stream, int clob) {
+  if (CM && clob) return EKAT_B200_ERR_UNSUPPORTED;
   constexpr int CPT = TmaCfg<R>::CPT, W = 32 * CPT, LB = TmaGeom<R, CM>::LB;
   const Tuning tu = tuning();
   const int nch = (nlev + LB - 1) / LB;
@@ -383,7 +423,7 @@ int tridiag_bfb_stream(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nma
   const size_t al = CM ? 1024 : 128;
   auto smem_for = [&](int stages) {
     const size_t hs = (((size_t)(2 * stages + 4 + nch) * 8 + 15) & ~(size_t)15) + 3 * 32 * sizeof(R) * CPT;  // barriers + hand-over state
-    return ((hs + al - 1) & ~(al - 1)) + (size_t)(nch + 3 * stages + 2) * chunk;
+    return ((hs + al - 1) & ~(al - 1)) + (size_t)(nch + 3 * stages + 2 + ((clob & 1) ? 2 : 0)) * chunk;
   };
   // tiles per SM: shared memory, and four CTAs of 96 threads x 150 registers fill the register file (capping the
   // registers at 128 for a fifth tile costs more than the tile brings: measured 77% against 82%)
@@ -400,8 +440,8 @@ int tridiag_bfb_stream(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nma
   const char* name = CM ? (f64 ? "tridiag_bfb_stream_cm<f64>" : "tridiag_bfb_stream_cm<f32>")
                         : (f64 ? "tridiag_bfb_stream<f64>" : "tridiag_bfb_stream<f32>");
 #define EKB_STREAM(NS_)                                                                                                    \
-  (pp ? launch_stream<R, NS_, CM, true>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem_for(NS_), stream, name) \
-      : launch_stream<R, NS_, CM, false>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem_for(NS_), stream, name))
+  (pp ? launch_stream<R, NS_, CM, true>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem_for(NS_), stream, name, clob) \
+      : launch_stream<R, NS_, CM, false>(dl, d, du, X, ncol, nlev, nmat, a_stride, x_stride, pd, smem_for(NS_), stream, name, clob))
   switch (ns) {
     case 2: return EKB_STREAM(2);
     case 3: return EKB_STREAM(3);
@@ -412,9 +452,9 @@ int tridiag_bfb_stream(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nma
 #undef EKB_STREAM
 }
 
-template int tridiag_bfb_stream<double, false>(double*, double*, double*, double*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
-template int tridiag_bfb_stream<float, false>(float*, float*, float*, float*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
-template int tridiag_bfb_stream<double, true>(double*, double*, double*, double*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
-template int tridiag_bfb_stream<float, true>(float*, float*, float*, float*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
+template int tridiag_bfb_stream<double, false>(double*, double*, double*, double*, int64_t, int, int, int64_t, int64_t, cudaStream_t, int);
+template int tridiag_bfb_stream<float, false>(float*, float*, float*, float*, int64_t, int, int, int64_t, int64_t, cudaStream_t, int);
+template int tridiag_bfb_stream<double, true>(double*, double*, double*, double*, int64_t, int, int, int64_t, int64_t, cudaStream_t, int);
+template int tridiag_bfb_stream<float, true>(float*, float*, float*, float*, int64_t, int, int, int64_t, int64_t, cudaStream_t, int);
 
 }  // namespace ekb

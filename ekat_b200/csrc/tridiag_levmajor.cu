@@ -31,6 +31,9 @@
 namespace ekb {
 
 // TMA-fed warp-per-tile kernel (tridiag_tma.cu); EKAT_B200_ERR_UNSUPPORTED if the operands do not qualify.
+template <typename R, bool CM>
+int tridiag_bfb_stream(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
+                       cudaStream_t stream, int clob);  // tridiag_bfb_stream.cu
 template <typename R>
 int tridiag_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride,
                 int64_t x_stride, cudaStream_t stream);
@@ -351,6 +354,13 @@ int tridiag_levmajor(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nle
   const bool split_ok = nA == 1 && !clobber && var_allows_shared(variant);
   if (split_ok && (nrhs > 1 || (!exact && sizeof(R) == 8) || var_forces_shared(variant))) {
     const int rc = tridiag_tma_shared<R>(exact, dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
+    if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+  }
+  if (nA == nrhs && clobber && variant == kVarAuto) {
+    // the in-place side effect (multipliers in dl(1..), pivots in d for bfb, :292-303; pivots in d for serial thomas,
+    // :216-227, which then runs the bfb sweep -- within its tolerance by construction): the input-only ring kernel
+    // stores the factorisation next to the solution (tridiag_bfb_stream.cu)
+    const int rc = tridiag_bfb_stream<R, false>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, stream, exact ? 3 : 2);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }
   if (nA == nrhs && !clobber && var_allows_warp_tile(variant)) {

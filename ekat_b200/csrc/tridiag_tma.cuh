@@ -109,6 +109,38 @@ __device__ __forceinline__ void bfb_fwd_chunk(const Vec<R, CPT> (&a)[LB], const 
     }
   }
 }
+// The same sweep that also hands out the multipliers (EKAT_B200_CLOBBER_DIAGS: the reference leaves them in dl(1..),
+// ekat_tridiag.hpp:299-300; dl(0) keeps what the caller put there).
+template <typename R, int CPT, int LB, bool SLOW>
+__device__ __forceinline__ void bfb_fwd_chunk_m(const Vec<R, CPT> (&a)[LB], const Vec<R, CPT> (&b)[LB], const Vec<R, CPT> (&c)[LB],
+                                                const Vec<R, CPT> (&x)[LB], Vec<R, CPT> (&o0)[LB], Vec<R, CPT> (&o1)[LB],
+                                                Vec<R, CPT> (&om)[LB], R (&dprev)[CPT], R (&xprev)[CPT], R (&uprev)[CPT], bool first,
+                                                bool& bad) {
+#pragma unroll
+  for (int u = 0; u < LB; ++u) {
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      R m;
+      if (SLOW) {
+        m = x_div(a[u].v[j], dprev[j]);
+      } else {
+        bool f = false;
+        m = div_spec(a[u].v[j], dprev[j], rcp_refined(dprev[j]), f);
+        if (u == 0) f = f && !first;
+        bad = bad || f;
+      }
+      om[u].v[j] = (u == 0 && first) ? a[u].v[j] : m;
+      if (u == 0) m = first ? (R)0 : m;
+      const R dc = x_sub(b[u].v[j], x_mul(m, uprev[j]));
+      const R xc = x_sub(x[u].v[j], x_mul(m, xprev[j]));
+      o0[u].v[j] = dc;
+      o1[u].v[j] = xc;
+      dprev[j] = dc;
+      xprev[j] = xc;
+      uprev[j] = c[u].v[j];
+    }
+  }
+}
 template <typename R, int CPT, int LB, bool SLOW>
 __device__ __forceinline__ void bfb_bwd_chunk(Vec<R, CPT> (&y)[LB], const Vec<R, CPT> (&dd)[LB], const Vec<R, CPT> (&ui)[LB],
                                               R (&xv)[CPT], bool& bad) {
@@ -144,6 +176,6 @@ struct TmaGeom<float, true> {
 // Returns EKAT_B200_ERR_UNSUPPORTED when a tile does not fit on chip.
 template <typename R, bool CM>
 int tridiag_bfb_stream(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
-                       cudaStream_t stream);
+                       cudaStream_t stream, int clob = 0);  // clob (level-major only): bit 0 multipliers -> dl, bit 1 pivots -> d
 
 }  // namespace ekb

@@ -404,3 +404,31 @@ def test_reference_layout_many_rhs(cuda, port, dt):
                         assert bits_equal(Aout[:, 1], Aref[:, 1])
                         assert bits_equal(Aout[:, 0, 1:], Aref[:, 0, 1:] if solver == "bfb" else A[:, 0, 1:])
                         assert bits_equal(Aout[:, 0, 0], A[:, 0, 0])  # dl(0) is never touched
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
+def test_clobber_level_major_stream(cuda, port, dt):
+    """EKAT_B200_CLOBBER_DIAGS on level-major operands with one matrix per right-hand side takes the input-only ring
+    kernel (tridiag_bfb_stream.cu), which stores the factorisation next to the solution: multipliers in dl(1..) and
+    pivots in d bit for bit as the reference's bfb leaves them (ekat_tridiag.hpp:292-303), dl(0) and du untouched;
+    thomas leaves the pivots in d (serial form, :216-227). Ragged top chunks, short and long columns, several
+    matrices per column, ragged last tiles."""
+    from ekat_b200._lib import lib
+    npdt, _ = DT[dt]
+    for nrow, nrhs, ncol in [(128, 1, 4099), (72, 1, 1000), (43, 1, 333), (129, 1, 700), (100, 3, 257), (8, 1, 64), (5, 2, 100),
+                             (1, 1, 40), (2, 1, 40), (200, 1, 130)]:
+        A, B = port.fill_tridiag(npdt, ncol, nrow, nrhs, nrhs, col0=3)
+        Aref, Xref = A.copy(), B.copy()
+        port.tridiag("bfb", Aref, Xref)
+        for solver in ("bfb", "thomas"):
+            got, Aout = run_gpu(solver, A, B, ekat_b200.LEV_MAJOR, cuda, clobber=True, pad=(-ncol) % 4)
+            name = lib().ekat_b200_last_kernel().decode()
+            assert name.startswith("tridiag_bfb_stream"), (name, nrow, nrhs)
+            assert bits_equal(got, Xref), (solver, nrow, nrhs, ncol)  # thomas runs the bfb sweep here
+            assert bits_equal(Aout[:, 2], A[:, 2]), "du untouched"
+            assert bits_equal(Aout[:, 1], Aref[:, 1]), "pivots in d"
+            assert bits_equal(Aout[:, 0, 0], A[:, 0, 0]), "dl(0) untouched"
+            if solver == "bfb":
+                assert bits_equal(Aout[:, 0, 1:], Aref[:, 0, 1:]), "multipliers in dl"
+            else:
+                assert bits_equal(Aout[:, 0], A[:, 0]), "serial thomas leaves dl alone"
