@@ -35,6 +35,9 @@ template <typename R, bool CM>
 int tridiag_bfb_stream(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride, int64_t x_stride,
                        cudaStream_t stream, int clob);  // tridiag_bfb_stream.cu
 template <typename R>
+int tridiag_bfb_shared(R* dl, R* d, R* du, R* X, const R* Xin, int64_t ncol, int nlev, int nrhs, int64_t a_stride, int64_t x_stride,
+                       cudaStream_t stream);  // tridiag_bfb_shared.cu
+template <typename R>
 int tridiag_tma(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nmat, int64_t a_stride,
                 int64_t x_stride, cudaStream_t stream);
 
@@ -349,6 +352,12 @@ int tridiag_levmajor(bool exact, R* dl, R* d, R* du, R* X, int64_t ncol, int nle
   // (tridiag_small.cu decides by shape whether it applies; kVarSmall forces it for tests and A/B measurements).
   if (!exact && nA == nrhs && !clobber && (variant == kVarAuto || variant == kVarSmall)) {
     const int rc = tridiag_small<R>(dl, d, du, X, ncol, nlev, nrhs, a_stride, x_stride, variant == kVarSmall, stream);
+    if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
+  }
+  if (exact && nA == 1 && nrhs > 1 && !clobber && variant == kVarAuto) {
+    // bfb, several right-hand sides sharing one matrix: forward sweeps and back-substitutions on different warps, so that
+    // item i+1 goes down the columns while item i comes back up (tridiag_bfb_shared.cu)
+    const int rc = tridiag_bfb_shared<R>(dl, d, du, X, X, ncol, nlev, nrhs, a_stride, x_stride, stream);
     if (rc != EKAT_B200_ERR_UNSUPPORTED) return rc;
   }
   const bool split_ok = nA == 1 && !clobber && var_allows_shared(variant);

@@ -281,11 +281,19 @@ def test_shared_matrix_persistent_many_items(cuda, port, dt, solver):
                              (129, 6, 148 * W * 2 + 3), (5, 3, 148 * W * 5 + 9), (8, 2, 148 * W * 3)]:
         A, B = port.fill_tridiag(npdt, ncol, nrow, 1, nrhs, col0=11)
         want = port.tridiag(solver, A.copy(), B.copy())
-        got, Aout = run_gpu(solver, A, B, ekat_b200.LEV_MAJOR, cuda, pad=(-ncol) % 4)  # TMA needs 16-byte pitches
         from ekat_b200._lib import lib
-        assert lib().ekat_b200_last_kernel().decode().startswith("tridiag_tma_shared"), lib().ekat_b200_last_kernel()
-        check(solver, got, want, npdt, (dt, nrow, nrhs, ncol))
-        assert bits_equal(Aout, A)
+        # default route (bfb: the split forward / backward kernel where it applies) and the persistent kernel with one
+        # warp per right-hand side pinned (variant 9)
+        for variant in (0, 9):
+            try:
+                lib().ekat_b200_set_tuning(0, 0, variant)
+                got, Aout = run_gpu(solver, A, B, ekat_b200.LEV_MAJOR, cuda, pad=(-ncol) % 4)  # TMA needs 16-byte pitches
+            finally:
+                lib().ekat_b200_set_tuning(0, 0, 0)
+            name = lib().ekat_b200_last_kernel().decode()
+            assert name.startswith("tridiag_tma_shared" if variant == 9 or solver == "thomas" else ("tridiag_bfb_shared", "tridiag_tma_shared")), name
+            check(solver, got, want, npdt, (dt, nrow, nrhs, ncol, variant))
+            assert bits_equal(Aout, A)
 
 
 @pytest.mark.parametrize("dt", ["f64", "f32"])
