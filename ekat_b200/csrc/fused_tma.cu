@@ -30,132 +30,10 @@
 #include <type_traits>
 
 #include "lin_interp_search.cuh"
-#include "tridiag_tma.cuh"
+#include "thomas_two_sided.cuh"
 
 namespace ekb {
 
-
-// ---- Elimination FROM BOTH ENDS ("burn at both ends", as tridiag_small.cu does for one right-hand side) ----------
-// The column is split at level M = 8 * ceil(nch / 2): levels 0 .. M-1 are eliminated downwards (the classical forward
-// sweep), levels nlev-1 .. M upwards (the same recurrence on the reversed system: du plays dl's part and vice versa);
-// the two halves meet in a 2x2 system for x(M-1), x(M), and the back-substitution runs outwards from there. Every thread
-// runs BOTH halves interleaved: two independent chains where there was one, so the dependent latency per column halves
-// at the same instruction count -- for the factor warp (whose ~8 K cycles per tile sit on the serial chain between two
-// tiles, see k_solve_remap_roles) and for every solver lane. Levels are taken 4 at a time per half (HS), operands of
-// both halves in registers before anything is stored. Levels past the end of a ragged last chunk are identity rows.
-// Agreement with the reference's one-sided Thomas: rounding level (diagonally dominant systems), as tridiag_small.cu.
-constexpr int kHS = 4;  // levels per half-step
-
-// level of slot s (0..7) of chunk k in processing order: ascending for the top half, descending for the bottom half
-template <bool UP>
-__device__ __forceinline__ int slot_level(int k, int s) { return k * kLB + (UP ? kLB - 1 - s : s); }
-
-// Factor, one half-step (4 slots) of each half; states (q1, q2, cp, gp) per half. In place: PM <- multipliers (coupling
-// to the level processed BEFORE: dl*g above, du*g below), PR <- 1/pivot, PC <- coupling to the level processed AFTER
-// times 1/pivot (c' above, a~' below).
-template <typename R, int TW>
-struct FacState {
-  R q1, q2, cp, gp;
-};
-template <typename R, int TW, bool UP, bool FULL>
-__device__ __forceinline__ void factor_load(const R* PM, const R* PR, const R* PC, int k, int s0, int nlev, int lc, R (&a)[kHS],
-                                            R (&b)[kHS], R (&c)[kHS]) {
-#pragma unroll
-  for (int u = 0; u < kHS; ++u) {
-    const int lev = slot_level<UP>(k, s0 + u);
-    const bool ok = FULL || lev < nlev;
-    const int o = (ok ? lev : 0) * TW + lc;
-    const R vl = PM[o], vd = PR[o], vu = PC[o];
-    a[u] = UP ? vu : vl;
-    c[u] = UP ? vl : vu;
-    b[u] = vd;
-    if (lev == 0) (UP ? c[u] : a[u]) = (R)0;          // dl(0) is never used (ekat_tridiag.hpp:24-27)
-    if (lev == nlev - 1) (UP ? a[u] : c[u]) = (R)0;   // du(nrow-1) is never used
-    if (!ok) {
-      a[u] = (R)0;
-      b[u] = (R)1;
-      c[u] = (R)0;
-    }
-  }
-}
-template <typename R, int TW, bool UP, bool FULL>
-__device__ __forceinline__ void factor_run(R* PM, R* PR, R* PC, int k, int s0, int nlev, int lc, const R (&a)[kHS], const R (&b)[kHS],
-                                           const R (&c)[kHS], FacState<R, TW>& st) {
-  constexpr int RN = TmaCfg<R>::RN;
-#pragma unroll
-  for (int u = 0; u < kHS; ++u) {
-    const int s = s0 + u;
-    R q;
-    if (s % RN == 0) q = f_fma(-(a[u] * st.cp), st.q2, b[u]);  // renormalised state: q[prev] == 1
-    else q = f_fma(b[u], st.q1, -((a[u] * st.cp) * st.q2));
-    const R rq = t_rcp(q);
-    const R g = (s % RN == 0) ? rq : st.q1 * rq;  // q[prev]/q[this] = 1/pivot
-    const int lev = slot_level<UP>(k, s);
-    if (FULL || lev < nlev) {
-      const int o = lev * TW + lc;
-      PM[o] = a[u] * st.gp;
-      PR[o] = g;
-      PC[o] = c[u] * g;
-    }
-    if ((s + 1) % RN == 0) {
-      st.q2 = g;
-      st.q1 = (R)1;
-    } else {
-      st.q2 = (s % RN == 0) ? (R)1 : st.q1;
-      st.q1 = q;
-    }
-    st.cp = c[u];
-    st.gp = g;
-  }
-}
-
-// Solver lane, way in (elimination of its right-hand side towards the middle): z = x - m*z_prev, stored as z * (1/pivot).
-template <typename R, int TW, bool UP, bool FULL>
-__device__ __forceinline__ void sweep_in_load(const R* PM, const R* PR, const R* px, int k, int s0, int nlev, int lc, R (&m)[kHS],
-                                              R (&g)[kHS], R (&x)[kHS]) {
-#pragma unroll
-  for (int u = 0; u < kHS; ++u) {
-    const int lev = slot_level<UP>(k, s0 + u);
-    const bool ok = FULL || lev < nlev;
-    const int o = (ok ? lev : 0) * TW;
-    m[u] = ok ? PM[o + lc] : (R)0;
-    g[u] = ok ? PR[o + lc] : (R)1;
-    x[u] = ok ? px[o] : (R)0;
-  }
-}
-template <typename R, int TW, bool UP, bool FULL>
-__device__ __forceinline__ void sweep_in_run(R* px, int k, int s0, int nlev, const R (&m)[kHS], const R (&g)[kHS], const R (&x)[kHS],
-                                             R& z) {
-#pragma unroll
-  for (int u = 0; u < kHS; ++u) {
-    z = f_fma(-m[u], z, x[u]);
-    const int lev = slot_level<UP>(k, s0 + u);
-    if (FULL || lev < nlev) px[lev * TW] = z * g[u];
-  }
-}
-// Way out (back-substitution from the middle): x = y - c*x_prev, slots of a chunk in REVERSE processing order.
-template <typename R, int TW, bool UP, bool FULL>
-__device__ __forceinline__ void sweep_out_load(const R* PC, const R* px, int k, int s0, int nlev, int lc, R (&c)[kHS], R (&y)[kHS]) {
-#pragma unroll
-  for (int u = 0; u < kHS; ++u) {
-    const int lev = slot_level<UP>(k, s0 + kHS - 1 - u);
-    const bool ok = FULL || lev < nlev;
-    const int o = (ok ? lev : 0) * TW;
-    c[u] = ok ? PC[o + lc] : (R)0;
-    y[u] = ok ? px[o] : (R)0;
-  }
-}
-template <typename R, int TW, bool UP, bool FULL>
-__device__ __forceinline__ void sweep_out_run(R* px, int k, int s0, int nlev, const R (&c)[kHS], const R (&y)[kHS], R& xv) {
-#pragma unroll
-  for (int u = 0; u < kHS; ++u) {
-    const int lev = slot_level<UP>(k, s0 + kHS - 1 - u);
-    if (FULL || lev < nlev) {
-      xv = f_fma(-c[u], xv, y[u]);
-      px[lev * TW] = xv;
-    }
-  }
-}
 
 // The role-split form (the default): no CTA-wide barrier after the prologue. NIW remap warps, NSW solver warps and one
 // factor warp each walk the CTA's tiles at their own pace and hand planes to each other through mbarriers:
@@ -186,7 +64,6 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
   const int warp = (NIW == 10 && NSW == 5) ? (int)((0xF987E654DB32CA10ull >> (4 * (tid >> 5))) & 15) : tid >> 5;
   const int lc = lane % TW, sub = lane / TW;
   const int nch = (nlev + LB - 1) / LB;
-  const int kt = (nch + 1) / 2, M = tmin(kt * LB, nlev);  // chunks of the top half; first level of the bottom half
   // barriers: [0] x1 landed, [1] dl+d+du landed, [2] factor planes free (NSW arrivals), then per rhs: landed[r],
   // solved[r], then per chunk: factored[k]; then the nrhs + 1 "last one out" counters
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);
@@ -254,26 +131,12 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
       }
       mbar_wait(&bars[1], par);
       if (hb < nlev) mbar_wait(bbar, par);  // both ends are needed at once
-      FacState<R, TW> ft = {(R)1, (R)0, (R)0, (R)0}, fb = {(R)1, (R)0, (R)0, (R)0};
-      auto factor_all = [&](auto full) {
-        constexpr bool FULL = decltype(full)::value;
-        for (int t = 0; t < kt; ++t) {
-          const int kb = nch - 1 - t;
-          const bool bot = kb >= kt;
-#pragma unroll
-          for (int s0 = 0; s0 < LB; s0 += kHS) {
-            R a0[kHS], b0[kHS], c0[kHS], a1[kHS], b1[kHS], c1[kHS];
-            factor_load<R, TW, false, FULL>(PM, PR, PC, t, s0, nlev, lc, a0, b0, c0);
-            if (bot) factor_load<R, TW, true, FULL>(PM, PR, PC, kb, s0, nlev, lc, a1, b1, c1);
-            factor_run<R, TW, false, FULL>(PM, PR, PC, t, s0, nlev, lc, a0, b0, c0, ft);
-            if (bot) factor_run<R, TW, true, FULL>(PM, PR, PC, kb, s0, nlev, lc, a1, b1, c1, fb);
-          }
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&fbar[t]);
-        }
+      auto done_step = [&](int t) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&fbar[t]);
       };
-      if (nlev % LB == 0) factor_all(std::true_type{});
-      else factor_all(std::false_type{});
+      if (nlev % LB == 0) two_sided_factor<R, true>(PM + lc, PR + lc, PC + lc, TW, nlev, done_step);
+      else two_sided_factor<R, false>(PM + lc, PR + lc, PC + lc, TW, nlev, done_step);
     }
   } else if (warp >= NIW) {
     // ================================================================ solver warps: lane = (rhs within the warp, column)
@@ -286,48 +149,9 @@ k_solve_remap_roles(const __grid_constant__ CUtensorMap mdl, const __grid_consta
         if (r < nrhs) {
           R* px = PX + (size_t)r * plane + lc;
           mbar_wait(&lbar[r], par);
-          auto sweeps = [&](auto full) {
-            constexpr bool FULL = decltype(full)::value;
-            R zt = (R)0, zb = (R)0;
-            for (int t = 0; t < kt; ++t) {  // way in, both halves interleaved
-              mbar_wait(&fbar[t], par);
-              const int kb = nch - 1 - t;
-              const bool bot = kb >= kt;
-#pragma unroll
-              for (int s0 = 0; s0 < LB; s0 += kHS) {
-                R m0[kHS], g0[kHS], x0[kHS], m1[kHS], g1[kHS], x1v[kHS];
-                sweep_in_load<R, TW, false, FULL>(PM, PR, px, t, s0, nlev, lc, m0, g0, x0);
-                if (bot) sweep_in_load<R, TW, true, FULL>(PM, PR, px, kb, s0, nlev, lc, m1, g1, x1v);
-                sweep_in_run<R, TW, false, FULL>(px, t, s0, nlev, m0, g0, x0, zt);
-                if (bot) sweep_in_run<R, TW, true, FULL>(px, kb, s0, nlev, m1, g1, x1v, zb);
-              }
-            }
-            if (M < nlev) {  // the two halves meet: x(M-1) + c'(M-1) x(M) = y(M-1),  a~'(M) x(M-1) + x(M) = y~(M)
-              const R ya = px[(M - 1) * TW], yb = px[M * TW], ca = PC[(M - 1) * TW + lc], ab = PC[M * TW + lc];
-              const R rdet = f_rcp(f_fma(-ca, ab, (R)1));
-              px[(M - 1) * TW] = f_fma(-ca, yb, ya) * rdet;  // the way out starts from x = 0 and finds these two in place
-              px[M * TW] = f_fma(-ab, ya, yb) * rdet;
-            }
-            R xt = (R)0, xb = (R)0;
-            for (int t = kt - 1; t >= 0; --t) {  // way out
-              const int kb = nch - 1 - t;
-              const bool bot = kb >= kt;
-#pragma unroll
-              for (int s0 = LB - kHS; s0 >= 0; s0 -= kHS) {
-                R c0[kHS], y0[kHS], c1[kHS], y1[kHS];
-                sweep_out_load<R, TW, false, FULL>(PC, px, t, s0, nlev, lc, c0, y0);
-                if (bot) sweep_out_load<R, TW, true, FULL>(PC, px, kb, s0, nlev, lc, c1, y1);
-                if (s0 == LB - kHS && M < nlev) {  // the interface levels are solved: no coupling beyond them
-                  if (t == kt - 1) c0[0] = (R)0;
-                  if (kb == kt) c1[0] = (R)0;
-                }
-                sweep_out_run<R, TW, false, FULL>(px, t, s0, nlev, c0, y0, xt);
-                if (bot) sweep_out_run<R, TW, true, FULL>(px, kb, s0, nlev, c1, y1, xb);
-              }
-            }
-          };
-          if (nlev % LB == 0) sweeps(std::true_type{});
-          else sweeps(std::false_type{});
+          auto wait_step = [&](int t) { mbar_wait(&fbar[t], par); };
+          if (nlev % LB == 0) two_sided_sweeps<R, true>(PM + lc, PR + lc, PC + lc, TW, px, TW, nlev, wait_step);
+          else two_sided_sweeps<R, false>(PM + lc, PR + lc, PC + lc, TW, px, TW, nlev, wait_step);
         }
         __syncwarp();
         if (r < nrhs && lc == 0) mbar_arrive(&sbar[r]);

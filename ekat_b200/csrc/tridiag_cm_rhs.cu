@@ -21,7 +21,7 @@
 // on the solver chains -- agreement to the tolerance; bfb: the reference's operation order with separately rounded
 // * - / -- bit-identical. EKAT_B200_CLOBBER_DIAGS: bfb leaves multipliers in dl(1..) and pivots in d as the
 // reference does (:292-303); thomas then runs the bfb sweep and writes back d only (serial thomas, :216-227).
-#include "tridiag_tma.cuh"
+#include "thomas_two_sided.cuh"
 
 namespace ekb {
 
@@ -137,57 +137,12 @@ k_tridiag_cm_rhs(const CmArgs a) {
           }
           hand_over(k);
         }
-      } else {  // ratio form: q1 = q[i-1], q2 = q[i-2], cp = du[i-1], gp = 1/pivot[i-1]; renormalised every RN levels
-        constexpr int RN = TmaCfg<R>::RN;
-        static_assert(kCmLB % RN == 0, "renormalisation interval must divide the chunk");
-        R q1 = 1, q2 = 0, cp = 0, gp = 0;
-        R va[kCmLB], vb[kCmLB], vc[kCmLB];
-        auto fetch = [&](int k) {  // operands of chunk k into registers (levels beyond the column repeat its first one)
-          const int i0 = k * kCmLB, n = nlev - i0;
-#pragma unroll
-          for (int u = 0; u < kCmLB; ++u) {
-            const int i = u < n ? i0 + u : i0;
-            va[u] = pl[i];
-            vb[u] = pd[i];
-            vc[u] = pu[i];
-          }
-        };
-        fetch(0);
-        va[0] = (R)0;  // dl(0) is never used (ekat_tridiag.hpp:24-27) and may hold anything
-        for (int k = 0; k < nch; ++k) {
-          const int i0 = k * kCmLB, n = nlev - i0;
-          R om[kCmLB], og[kCmLB], oc[kCmLB];
-#pragma unroll
-          for (int u = 0; u < kCmLB; ++u) {
-            R q;
-            if (u % RN == 0) q = f_fma(-(va[u] * cp), q2, vb[u]);  // renormalised state: q[i-1] == 1
-            else q = f_fma(vb[u], q1, -((va[u] * cp) * q2));
-            const R rq = t_rcp(q);
-            const R g = (u % RN == 0) ? rq : q1 * rq;  // q[i-1]/q[i] = 1/pivot[i]
-            om[u] = va[u] * gp;                         // multiplier dl[i]/pivot[i-1]
-            og[u] = g;
-            oc[u] = (i0 + u == nlev - 1) ? (R)0 : vc[u] * g;  // du(nrow-1) is never used
-            if ((u + 1) % RN == 0) {
-              q2 = g;
-              q1 = (R)1;
-            } else {
-              q2 = (u % RN == 0) ? (R)1 : q1;
-              q1 = q;
-            }
-            cp = vc[u];
-            gp = g;
-          }
-          if (k + 1 < nch) fetch(k + 1);  // the next chunk's operands are on their way while this one is stored
-#pragma unroll
-          for (int u = 0; u < kCmLB; ++u) {
-            if (u < n) {
-              pl[i0 + u] = om[u];
-              pd[i0 + u] = og[u];
-              pu[i0 + u] = oc[u];
-            }
-          }
-          hand_over(k);
-        }
+      } else {
+        // thomas: ratio form (no division on the dependent chain), FROM BOTH ENDS -- the factor lane runs the downward
+        // recurrence of the top half and the upward one of the bottom half interleaved (thomas_two_sided.cuh), one
+        // hand-over per step = chunk t from the top and chunk nch-1-t from the bottom
+        if (nlev % kCmLB == 0) two_sided_factor<R, true>(pl, pd, pu, 1, nlev, hand_over);
+        else two_sided_factor<R, false>(pl, pd, pu, 1, nlev, hand_over);
       }
     }
   } else {
@@ -200,7 +155,12 @@ k_tridiag_cm_rhs(const CmArgs a) {
       R* pd = pl + a.PP;
       R* pu = pd + a.PP;
       const int sa = nA, sx = nrhs;  // element strides between levels
-      if (nA == 1) {
+      if (nA == 1 && !EXACT) {
+        // both sweeps from both ends, a step behind the factor lane of this column
+        auto wait_step = [&](int t) { mbar_wait(&cb[t], 0u); };
+        if (nlev % kCmLB == 0) two_sided_sweeps<R, true>(pl, pd, pu, 1, px, sx, nlev, wait_step);
+        else two_sided_sweeps<R, false>(pl, pd, pu, 1, px, sx, nlev, wait_step);
+      } else if (nA == 1) {
         // forward sweep a chunk behind the factor lane of this column
         R z = 0;
         for (int i0 = 0; i0 < nlev; i0 += kCmLB) {
@@ -281,8 +241,9 @@ k_tridiag_cm_rhs(const CmArgs a) {
           }
         }
       }
-      // back substitution
-      if (EXACT) {  // :317-319  X(n-1) /= d(n-1); X(i) = (X(i) - du(i)*X(i+1)) / d(i)
+      // back substitution (the two-sided path has done its own)
+      if (nA == 1 && !EXACT) {
+      } else if (EXACT) {  // :317-319  X(n-1) /= d(n-1); X(i) = (X(i) - du(i)*X(i+1)) / d(i)
         R xv = x_div(px[(nlev - 1) * sx], pd[(nlev - 1) * sa]);
         px[(nlev - 1) * sx] = xv;
         int i = nlev - 2;
