@@ -241,6 +241,183 @@ k_tridiag_cr_warp(const CrwArgs a) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Columns longer than one warp holds (257 .. 2,048 levels, one right-hand side): the same scheme with NW = 2, 4 or 8
+// warps per column -- "few columns, many levels", the shape cyclic reduction exists for (reference guidance
+// src/algorithm/ekat_tridiag.hpp:71-74; the reference's own test runs nrow = 2048,
+// tests/algorithm/tridiag_tests_correctness.cpp:410-414). Thread t of the CTA owns rows 8t .. 8t+7 in registers. A level
+// needs at most ONE row from another warp: the left neighbour of a warp's lane 0 (on the way down) or the right
+// neighbour of its last active lane (on the way up); levels whose offset is a multiple of 256 rows involve lane 0 of
+// the warps only. That one row per warp and level goes through a small shared-memory array (two copies, alternating by
+// level, so one __syncthreads per level is enough); everything else stays in registers and travels by shuffle.
+constexpr int kCtaRPT = 8;
+
+template <typename R, bool LM>
+__global__ void __launch_bounds__(256)
+k_tridiag_cr_cta(const CrwArgs a) {
+  constexpr int RPT = kCtaRPT;
+  using Row = CrwRow<R, 1>;
+  __shared__ Row edge[2][8];
+  __shared__ R xedge[2][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, t = threadIdx.x, NW = blockDim.x >> 5;
+  const int64_t col = blockIdx.x;
+  const int nrow = a.nlev;
+  const R* gl = static_cast<const R*>(a.dl);
+  const R* gd = static_cast<const R*>(a.d);
+  const R* gu = static_cast<const R*>(a.du);
+  R* gx = static_cast<R*>(a.X);
+  auto off = [&](int i, int64_t stride) { return LM ? (size_t)i * stride + col : (size_t)col * stride + i; };
+
+  Row row[RPT];
+#pragma unroll
+  for (int k = 0; k < RPT; ++k) {
+    const int i = RPT * t + k;
+    const bool ok = i < nrow;
+    row[k].l = ok ? __ldg(gl + off(i, a.a_stride)) : (R)0;
+    row[k].d = ok ? __ldg(gd + off(i, a.a_stride)) : (R)1;
+    row[k].u = ok ? __ldg(gu + off(i, a.a_stride)) : (R)0;
+    row[k].x[0] = ok ? gx[off(i, a.x_stride)] : (R)0;
+  }
+  int lv = 0, os = 1;
+  // ------------------------------------------------------------------ way down :401-423
+#pragma unroll
+  for (int ls = 1; ls < RPT; ls <<= 1) {  // offsets inside a thread; local row 0 takes its left neighbour from thread t-1
+    if (2 * ls < nrow) {
+      if (lane == 31) edge[lv & 1][warp] = row[RPT - ls];
+      __syncthreads();
+      Row hl = crw_shfl_up(row[RPT - ls], 1);
+      if (lane == 0 && warp > 0) hl = edge[lv & 1][warp - 1];
+#pragma unroll
+      for (int k = 0; k < RPT; k += 2 * ls) {
+        const int i = RPT * t + k;
+        const bool im_ok = i - ls >= 0, ip_ok = i + ls < nrow;
+        const Row n = crw_down<R, 1>(row[k], k == 0 ? hl : row[k >= ls ? k - ls : 0], row[k + ls], im_ok, ip_ok);
+        if (i < nrow) row[k] = n;
+      }
+      os = 2 * ls;
+      ++lv;
+    }
+  }
+#pragma unroll
+  for (int s = 1; s < 32; s <<= 1) {  // offsets of s threads inside a warp
+    if (2 * RPT * s < nrow) {
+      if (lane == 32 - s) edge[lv & 1][warp] = row[0];
+      __syncthreads();
+      Row m = crw_shfl_up(row[0], s);
+      const Row p = crw_shfl_down(row[0], s);
+      if (lane == 0 && warp > 0) m = edge[lv & 1][warp - 1];
+      const int i = RPT * t;
+      const bool im_ok = t >= s, ip_ok = lane + s < 32 && i + RPT * s < nrow;
+      const Row n = crw_down<R, 1>(row[0], m, p, im_ok, ip_ok);
+      if ((lane & (2 * s - 1)) == 0 && i < nrow) row[0] = n;
+      os = 2 * RPT * s;
+      ++lv;
+    }
+  }
+  for (int sw = 1; sw < NW; sw <<= 1) {  // offsets of sw warps: lane 0 of the warps that are multiples of 2 sw
+    if (2 * RPT * 32 * sw < nrow) {
+      if (lane == 0) edge[lv & 1][warp] = row[0];
+      __syncthreads();
+      const int i = RPT * t;
+      if (lane == 0 && (warp & (2 * sw - 1)) == 0 && i < nrow) {
+        const bool im_ok = warp >= sw, ip_ok = warp + sw < NW && i + RPT * 32 * sw < nrow;
+        const Row m = edge[lv & 1][im_ok ? warp - sw : warp], p = edge[lv & 1][ip_ok ? warp + sw : warp];
+        row[0] = crw_down<R, 1>(row[0], m, p, im_ok, ip_ok);
+      }
+      os = 2 * RPT * 32 * sw;
+      ++lv;
+    }
+  }
+  // ------------------------------------------------------------------ rows 0 and os are what is left (:427-437)
+  {
+    const int ts = os / RPT, ks = os % RPT;  // owner of row os
+    if (t == 0) edge[lv & 1][0] = row[0];
+    if (os < nrow && t == ts) {
+      Row mine = row[0];
+#pragma unroll
+      for (int k = 1; k < RPT; ++k)
+        if (k == ks) mine = row[k];
+      edge[lv & 1][1] = mine;
+    }
+    __syncthreads();
+    if (t == 0 || (os < nrow && t == ts)) {
+      const Row r0 = edge[lv & 1][0];
+      if (os >= nrow) {
+        row[0].x[0] = x_div(r0.x[0], r0.d);
+      } else {
+        const Row rs = edge[lv & 1][1];
+        const R det = x_sub(x_mul(r0.d, rs.d), x_mul(r0.u, rs.l));
+        const R xa = x_div(x_sub(x_mul(rs.d, r0.x[0]), x_mul(r0.u, rs.x[0])), det);
+        const R xb = x_div(x_sub(x_mul(r0.d, rs.x[0]), x_mul(rs.l, r0.x[0])), det);
+        if (t == 0) row[0].x[0] = xa;
+        if (t == ts) {
+#pragma unroll
+          for (int k = 0; k < RPT; ++k)
+            if (k == ks) row[k].x[0] = xb;
+        }
+      }
+    }
+    ++lv;
+  }
+  // ------------------------------------------------------------------ way up :442-457 (only solution values travel)
+  for (int sw = NW >> 1; sw >= 1; sw >>= 1) {
+    if (2 * RPT * 32 * sw <= os) {
+      if (lane == 0) xedge[lv & 1][warp] = row[0].x[0];
+      __syncthreads();
+      const int i = RPT * t;
+      if (lane == 0 && (warp & (2 * sw - 1)) == sw && i < nrow) {
+        const bool ip_ok = warp + sw < NW && i + RPT * 32 * sw < nrow;
+        const R xm[1] = {xedge[lv & 1][warp - sw]}, xp[1] = {xedge[lv & 1][ip_ok ? warp + sw : warp]};
+        crw_up<R, 1>(row[0], xm, xp, ip_ok);
+      }
+      ++lv;
+    }
+  }
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    if (2 * RPT * s <= os) {
+      if (lane == 0) xedge[lv & 1][warp] = row[0].x[0];  // the right neighbour of a warp's lane 32-s is the next warp's lane 0
+      __syncthreads();
+      R xm[1], xp[1];
+      xm[0] = __shfl_up_sync(0xffffffffu, row[0].x[0], s);
+      xp[0] = __shfl_down_sync(0xffffffffu, row[0].x[0], s);
+      if (lane + s >= 32) xp[0] = xedge[lv & 1][warp + 1 < NW ? warp + 1 : warp];
+      const int i = RPT * t;
+      const bool ip_ok = i + RPT * s < nrow;
+      Row n = row[0];
+      crw_up<R, 1>(n, xm, xp, ip_ok);
+      if ((lane & (2 * s - 1)) == s && i < nrow) row[0] = n;
+      ++lv;
+    }
+  }
+#pragma unroll
+  for (int ls = RPT / 2; ls >= 1; ls >>= 1) {
+    if (2 * ls <= os) {
+      if (lane == 0) xedge[lv & 1][warp] = row[0].x[0];
+      __syncthreads();
+      R xr[1];  // local row 0 of the next thread: the right neighbour of the thread's last row of this level
+      xr[0] = __shfl_down_sync(0xffffffffu, row[0].x[0], 1);
+      if (lane == 31) xr[0] = xedge[lv & 1][warp + 1 < NW ? warp + 1 : warp];
+#pragma unroll
+      for (int k = ls; k < RPT; k += 2 * ls) {
+        const int i = RPT * t + k;
+        const bool ip_ok = i + ls < nrow;
+        R xp[1];
+        xp[0] = k + ls < RPT ? row[k + ls < RPT ? k + ls : 0].x[0] : xr[0];
+        Row n = row[k];
+        crw_up<R, 1>(n, row[k - ls].x, xp, ip_ok);
+        if (i < nrow) row[k] = n;
+      }
+      ++lv;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < RPT; ++k) {
+    const int i = RPT * t + k;
+    if (i < nrow) gx[off(i, a.x_stride)] = row[k].x[0];
+  }
+}
+
 template <typename R, int RPT, int G, bool LM>
 static int launch_cr_warp(const CrwArgs& a, cudaStream_t stream) {
   const int64_t nwarps = a.ncol * a.ngroups;
@@ -251,12 +428,25 @@ static int launch_cr_warp(const CrwArgs& a, cudaStream_t stream) {
   return check_cuda(cudaGetLastError());
 }
 
-// Returns EKAT_B200_ERR_UNSUPPORTED for more than 256 levels (a column no longer fits the registers of one warp).
+// Up to 256 levels: one warp per (column, rhs group); up to 2,048 levels and one right-hand side: 2 .. 8 warps per
+// column. Returns EKAT_B200_ERR_UNSUPPORTED beyond that.
 template <typename R>
 int tridiag_cr_warp(R* dl, R* d, R* du, R* X, int64_t ncol, int nlev, int nrhs, int64_t a_stride, int64_t x_stride,
                     int layout, cudaStream_t stream) {
-  if (nlev > 256) return EKAT_B200_ERR_UNSUPPORTED;
   const bool lm = layout == EKAT_B200_LAYOUT_LEV_MAJOR;
+  if (nlev > 256) {  // several warps per column
+    if (nlev > 256 * kCtaRPT || nrhs != 1 || ncol >= (int64_t)1 << 31) return EKAT_B200_ERR_UNSUPPORTED;
+    int nw = 2;
+    while (nw * 32 * kCtaRPT < nlev) nw *= 2;
+    CrwArgs a;
+    a.dl = dl; a.d = d; a.du = du; a.X = X;
+    a.ncol = ncol; a.a_stride = a_stride; a.x_stride = x_stride;
+    a.nlev = nlev; a.nrhs = 1; a.ngroups = 1;
+    if (lm) k_tridiag_cr_cta<R, true><<<(unsigned)ncol, 32 * nw, 0, stream>>>(a);
+    else k_tridiag_cr_cta<R, false><<<(unsigned)ncol, 32 * nw, 0, stream>>>(a);
+    note_launch(sizeof(R) == 8 ? (lm ? "tridiag_cr_cta<f64>" : "tridiag_cr_cta_cm<f64>") : (lm ? "tridiag_cr_cta<f32>" : "tridiag_cr_cta_cm<f32>"));
+    return check_cuda(cudaGetLastError());
+  }
   // level-major operands are read with a stride here: with one right-hand side that only pays for small batches
   // (B200, f64, 128 levels: 2,048 columns 11 us against the tile kernel's 15; 4,736 columns 24 against 16)
   if (lm && nrhs == 1 && (ncol > 2048 || nlev > 128)) return EKAT_B200_ERR_UNSUPPORTED;
