@@ -21,6 +21,7 @@ for _t in ("f64", "f32"):
     _SIGS[f"ekat_b200_lin_interp_setup_{_t}"] = [vp, vp, vp, i64, cint, cint, i64, i64, vp]
     _SIGS[f"ekat_b200_lin_interp_apply_{_t}"] = [vp, vp, vp, vp, vp, i64, cint, cint, i64, i64, cint, i64, i64, vp]
     _SIGS[f"ekat_b200_lin_interp_{_t}"] = [vp, vp, vp, vp, vp, i64, cint, cint, i64, i64, cint, i64, i64, vp]
+    _SIGS[f"ekat_b200_lin_interp_static_map_{_t}"] = [vp, vp, vp, vp, i64, cint, cint, i64, i64, cint, i64, i64, vp]
     _SIGS[f"ekat_b200_lin_interp_lm_{_t}"] = [vp, vp, vp, vp, i64, cint, cint, i64, cint, vp]
     _SIGS[f"ekat_b200_tridiag_lin_interp_{_t}"] = [vp, vp, vp, vp, vp, vp, vp, vp, i64, cint, cint, cint, i64, vp]
     _SIGS[f"ekat_b200_col_to_lev_{_t}"] = [vp, vp, i64, cint, i64, i64, vp]

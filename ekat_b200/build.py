@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libekat_b200.so")
-SOURCES = ["capi.cu", "tridiag_levmajor.cu", "tridiag_tma.cu", "tridiag_tma_shared.cu", "tridiag_small.cu", "tridiag_bfb_stream.cu", "tridiag_bfb_shared.cu", "tridiag_tile.cu", "tridiag_cm_rhs.cu", "tridiag_cr_tma.cu", "tridiag_cr_warp.cu", "lin_interp.cu", "lin_interp_lm.cu", "fused.cu", "fused_tma.cu", "util.cu", "view_reduction.cu", "column_ops.cu", "host_pipeline.cu"]
+SOURCES = ["capi.cu", "tridiag_levmajor.cu", "tridiag_tma.cu", "tridiag_tma_shared.cu", "tridiag_small.cu", "tridiag_bfb_stream.cu", "tridiag_bfb_shared.cu", "tridiag_tile.cu", "tridiag_cm_rhs.cu", "tridiag_cr_tma.cu", "tridiag_cr_warp.cu", "lin_interp.cu", "lin_interp_lm.cu", "fused.cu", "fused_tma.cu", "util.cu", "view_reduction.cu", "column_ops.cu", "host_pipeline.cu", "no_alloc.cu"]
 HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "tridiag_lm_common.cuh"), os.path.join(CSRC, "tridiag_tma.cuh"), os.path.join(CSRC, "thomas_two_sided.cuh"), os.path.join(CSRC, "lin_interp_search.cuh"), os.path.join(HERE, "..", "include", "ekat_b200", "ekat_b200.h")]
 NVCC = os.environ.get("EKAT_B200_NVCC", "nvcc")
 # sm_100a only (no PTX for other archs, no multi-arch fatbin). -lineinfo for ncu source pages.

@@ -97,6 +97,10 @@ int check_cuda(cudaError_t e) {
   t_err[sizeof(t_err) - 1] = 0;
   return EKAT_B200_ERR_CUDA;
 }
+void set_error_text(const char* text) {
+  std::strncpy(t_err, text, sizeof(t_err) - 1);
+  t_err[sizeof(t_err) - 1] = 0;
+}
 Tuning tuning() { return t_tuning; }
 
 // (kernel, device) -> largest dynamic shared memory size already granted by cudaFuncSetAttribute. The attribute

@@ -166,6 +166,25 @@ int ekat_b200_lin_interp_lm_f64(const double* x1, const double* x2, const double
 int ekat_b200_lin_interp_lm_f32(const float* x1, const float* x2, const float* y1, float* y2, int64_t ncol, int km1,
                                 int km2, int64_t pitch, int nfields, ekat_b200_stream_t stream);
 
+/* LinInterp::setup + LinInterp::lin_interp WITHOUT a caller-owned index map and without any allocation.
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). Arguments, layout and
+ * results are those of ekat_b200_lin_interp_* above (bit-identical y2); the index map lives in a file-scope device
+ * array of EKAT_B200_STATIC_MAP_MAX_ENTRIES ints (16 MiB, held by every GPU that loads the library until exit):
+ *   - ncol*km2 > EKAT_B200_STATIC_MAP_MAX_ENTRIES returns EKAT_B200_ERR_TOO_LARGE (text in
+ *     ekat_b200_last_cuda_error()); use ekat_b200_lin_interp_* with your own map then;
+ *   - every call on a device shares the array, which keeps the previous call's contents (each call overwrites all
+ *     entries it reads, nothing needs clearing); calls that OVERLAP on the GPU -- different streams with no
+ *     dependency between them -- race on it and must be serialised by the caller;
+ *   - calls no cudaMalloc / cudaFree / allocating library routine (ekat_b200/csrc/no_alloc.cu). */
+#define EKAT_B200_STATIC_MAP_MAX_ENTRIES 4194304
+int ekat_b200_lin_interp_static_map_f64(const double* x1, const double* x2, const double* y1, double* y2, int64_t ncol,
+                                        int km1, int km2, int64_t pitch1, int64_t pitch2, int nfields,
+                                        int64_t y1_fstride, int64_t y2_fstride, ekat_b200_stream_t stream);
+int ekat_b200_lin_interp_static_map_f32(const float* x1, const float* x2, const float* y1, float* y2, int64_t ncol,
+                                        int km1, int km2, int64_t pitch1, int64_t pitch2, int nfields,
+                                        int64_t y1_fstride, int64_t y2_fstride, ekat_b200_stream_t stream);
+
 /* ------------------------------------------------------------------------
  * Layout marshalling: [ncol][n] <-> [n][pitch] device
  * transposes at copy speed, so callers holding reference-layout views can use
