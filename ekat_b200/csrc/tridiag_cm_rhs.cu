@@ -102,13 +102,16 @@ k_tridiag_cm_rhs(const CmArgs a) {
           const R sd = dprev, su = uprev;
           R om[kCmLB], od[kCmLB];
           bool bad = false;
+          R rp = rcp_seed(dprev);  // ~ 1 / d'(i-1): reciprocal of the PREDICTED pivot, off the chain (common.cuh bfb_pivot_step)
 #pragma unroll
           for (int u = 0; u < kCmLB; ++u) {
             bool f = false;
-            const R m = div_spec(va[u], dprev, rcp_refined(dprev), f);
+            R dn = dprev, rn = rp;
+            const R m = bfb_pivot_step(va[u], vb[u], uprev, dn, rn, f);
             bad = bad || (f && i0 + u > 0 && u < n);
             if (i0 + u > 0) {
-              dprev = x_sub(vb[u], x_mul(m, uprev));
+              dprev = dn;
+              rp = rn;
               uprev = vc[u];
             }
             om[u] = m;

@@ -85,21 +85,24 @@ template <typename R, int CPT, int LB, bool SLOW>
 __device__ __forceinline__ void bfb_fwd_chunk(const Vec<R, CPT> (&a)[LB], const Vec<R, CPT> (&b)[LB], const Vec<R, CPT> (&c)[LB],
                                               const Vec<R, CPT> (&x)[LB], Vec<R, CPT> (&o0)[LB], Vec<R, CPT> (&o1)[LB],
                                               R (&dprev)[CPT], R (&xprev)[CPT], R (&uprev)[CPT], bool first, bool& bad) {
+  R rp[CPT];  // ~ 1 / d'(i-1): reciprocal of the PREDICTED pivot, off the chain (common.cuh bfb_pivot_step)
+  if (!SLOW) {
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) rp[j] = rcp_seed(dprev[j]);
+  }
 #pragma unroll
   for (int u = 0; u < LB; ++u) {
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
-      R m;
+      const R av = (u == 0 && first) ? (R)0 : a[u].v[j];  // dl(0) is never used (ekat_tridiag.hpp:24-27)
+      R m, dc;
       if (SLOW) {
-        m = x_div(a[u].v[j], dprev[j]);
+        m = (u == 0 && first) ? (R)0 : x_div(av, dprev[j]);
+        dc = x_sub(b[u].v[j], x_mul(m, uprev[j]));        // d(i) -= dl(i)*du(i-1)      :301
       } else {
-        bool f = false;
-        m = div_spec(a[u].v[j], dprev[j], rcp_refined(dprev[j]), f);
-        if (u == 0) f = f && !first;  // level 0 of a column has no multiplier
-        bad = bad || f;
+        dc = dprev[j];
+        m = bfb_pivot_step(av, b[u].v[j], uprev[j], dc, rp[j], bad);
       }
-      if (u == 0) m = first ? (R)0 : m;                   // dl(0) is never used (ekat_tridiag.hpp:24-27)
-      const R dc = x_sub(b[u].v[j], x_mul(m, uprev[j]));  // d(i) -= dl(i)*du(i-1)      :301
       const R xc = x_sub(x[u].v[j], x_mul(m, xprev[j]));  // X(i) -= dl(i)*X(i-1)       :315-316
       o0[u].v[j] = dc;
       o1[u].v[j] = xc;
@@ -116,22 +119,25 @@ __device__ __forceinline__ void bfb_fwd_chunk_m(const Vec<R, CPT> (&a)[LB], cons
                                                 const Vec<R, CPT> (&x)[LB], Vec<R, CPT> (&o0)[LB], Vec<R, CPT> (&o1)[LB],
                                                 Vec<R, CPT> (&om)[LB], R (&dprev)[CPT], R (&xprev)[CPT], R (&uprev)[CPT], bool first,
                                                 bool& bad) {
+  R rp[CPT];
+  if (!SLOW) {
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) rp[j] = rcp_seed(dprev[j]);
+  }
 #pragma unroll
   for (int u = 0; u < LB; ++u) {
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
-      R m;
+      const R av = (u == 0 && first) ? (R)0 : a[u].v[j];
+      R m, dc;
       if (SLOW) {
-        m = x_div(a[u].v[j], dprev[j]);
+        m = (u == 0 && first) ? (R)0 : x_div(av, dprev[j]);
+        dc = x_sub(b[u].v[j], x_mul(m, uprev[j]));
       } else {
-        bool f = false;
-        m = div_spec(a[u].v[j], dprev[j], rcp_refined(dprev[j]), f);
-        if (u == 0) f = f && !first;
-        bad = bad || f;
+        dc = dprev[j];
+        m = bfb_pivot_step(av, b[u].v[j], uprev[j], dc, rp[j], bad);
       }
       om[u].v[j] = (u == 0 && first) ? a[u].v[j] : m;
-      if (u == 0) m = first ? (R)0 : m;
-      const R dc = x_sub(b[u].v[j], x_mul(m, uprev[j]));
       const R xc = x_sub(x[u].v[j], x_mul(m, xprev[j]));
       o0[u].v[j] = dc;
       o1[u].v[j] = xc;

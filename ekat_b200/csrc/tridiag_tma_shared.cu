@@ -42,21 +42,24 @@ template <typename R, int CPT, int LB, bool SLOW>
 __device__ __forceinline__ void bfb_factor_chunk(const Vec<R, CPT> (&a)[LB], const Vec<R, CPT> (&b)[LB], const Vec<R, CPT> (&c)[LB],
                                                  Vec<R, CPT> (&om)[LB], Vec<R, CPT> (&od)[LB], R (&dprev)[CPT], R (&uprev)[CPT],
                                                  bool first, bool& bad) {
+  R rp[CPT];  // ~ 1 / d'(i-1): reciprocal of the PREDICTED pivot, off the chain (common.cuh bfb_pivot_step)
+  if (!SLOW) {
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) rp[j] = rcp_seed(dprev[j]);
+  }
 #pragma unroll
   for (int u = 0; u < LB; ++u) {
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
-      R m;
+      const R av = (u == 0 && first) ? (R)0 : a[u].v[j];  // dl(0) is never used (:24-27)
+      R m, dc;
       if (SLOW) {
-        m = x_div(a[u].v[j], dprev[j]);
+        m = (u == 0 && first) ? (R)0 : x_div(av, dprev[j]);
+        dc = x_sub(b[u].v[j], x_mul(m, uprev[j]));        // d(i) -= dl(i)*du(i-1)   :301
       } else {
-        bool f = false;
-        m = div_spec(a[u].v[j], dprev[j], rcp_refined(dprev[j]), f);
-        if (u == 0) f = f && !first;
-        bad = bad || f;
+        dc = dprev[j];
+        m = bfb_pivot_step(av, b[u].v[j], uprev[j], dc, rp[j], bad);
       }
-      if (u == 0) m = first ? (R)0 : m;                   // dl(0) is never used (:24-27)
-      const R dc = x_sub(b[u].v[j], x_mul(m, uprev[j]));  // d(i) -= dl(i)*du(i-1)   :301
       om[u].v[j] = m;
       od[u].v[j] = dc;
       dprev[j] = dc;

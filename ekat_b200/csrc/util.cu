@@ -251,6 +251,7 @@ __global__ void k_residual(const R* __restrict__ dl, const R* __restrict__ d, co
 // x_div_pipelined (reciprocal hoisted, common.cuh) against the compiler's IEEE division on random operands:
 // mode 0 = random bit patterns (every exponent, denormals, infinities, NaNs excluded from the count when both
 // results are NaN), mode 1 = operands in the well-scaled range the solvers see. Counts bitwise mismatches.
+// modes 2 / 3: the same two operand populations through the certified quotient (see below); 4 / 5: its flag rate.
 template <typename R> struct DivRef;
 template <> struct DivRef<double> {
   using U = unsigned long long;
@@ -270,12 +271,32 @@ __global__ void k_selftest_div(uint64_t n, uint64_t seed, int mode, unsigned lon
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
     const uint64_t ra = splitmix64(seed + 2 * i), rb = splitmix64(seed + 2 * i + 1);
     R a, b;
-    if (mode == 0) {
+    if ((mode & 1) == 0) {
       a = DivRef<R>::make(ra);
       b = DivRef<R>::make(rb);
     } else {
       a = (R)(((double)(ra >> 11) * (1.0 / 9007199254740992.0) - 0.5) * 200.0);
       b = (R)(((double)(rb >> 11) * (1.0 / 9007199254740992.0) + 0.01) * ((rb & 1) ? 60.0 : -60.0));
+    }
+    if (mode >= 2) {
+      // modes 2, 3: the certified quotient of the bfb factorisation (common.cuh bfb_pivot_step) with a reciprocal taken
+      // of a PERTURBED divisor (the predicted pivot: a few ulp to 2^-30 away) must be right whenever it is not flagged;
+      // modes 4, 5: count the flags instead (how often the full-range redo would run)
+      const uint64_t rp = splitmix64(seed ^ (0x9e3779b97f4a7c15ull * (i + 1)));
+      const int sh = mode >= 6 ? 1 : (int)(rp & 31);  // perturbation 2^-53 .. 2^-22 relative (modes 6, 7: 2^-52, flag counts)
+      const R bp = b * ((R)1 + (R)((rp >> 8 & 1) ? 1 : -1) * (R)ldexp(1.0, -(sizeof(R) == 8 ? 53 : 24) + (sizeof(R) == 8 ? sh : sh % 12)));
+      for (int z = 0; z < 2; ++z) {
+        const R an = z ? (R)0 : a;
+        const R r = rcp_seed(bp);
+        const R q0 = x_mul(an, r);
+        const R m = fma(r, fma(-b, q0, an), q0);
+        bool flagged = false;
+        certify_quotient(an, b, m, flagged);
+        const R ws = DivRef<R>::ref(an, b);
+        if (mode >= 4) bad += flagged ? 1 : 0;
+        else if (!flagged && DivRef<R>::bits(m) != DivRef<R>::bits(ws) && !(m != m && ws != ws)) ++bad;
+      }
+      continue;
     }
     const R q = x_div_pipelined(a, b), w = DivRef<R>::ref(a, b);
     if (DivRef<R>::bits(q) != DivRef<R>::bits(w) && !(q != q && w != w)) ++bad;

@@ -197,6 +197,16 @@ def test_pipelined_division_is_ieee(cuda, dt):
         check("selftest_div", fn(1 << 28, 12345 + mode, mode, out.data_ptr(), None))
     torch.cuda.synchronize()
     assert int(out.item()) == 0
+    # the certified quotient of the bfb factorisation (reciprocal of a PREDICTED pivot, common.cuh bfb_pivot_step): right
+    # whenever its certificate does not send the chunk to the full-range division, for reciprocals up to 2^-22 off
+    for mode in (2, 3):
+        check("selftest_div", fn(1 << 27, 777 + mode, mode, out.data_ptr(), None))
+    torch.cuda.synchronize()
+    assert int(out.item()) == 0
+    # ... and with a prediction as close as the recurrence's (2^-52), well-scaled operands (almost) never need the redo
+    check("selftest_div", fn(1 << 26, 4242, 7, out.data_ptr(), None))
+    torch.cuda.synchronize()
+    assert int(out.item()) <= 64, int(out.item())  # of 2^27 quotients (f32: MUFU.RCP's last bit; f64: none seen)
 
 
 def test_odd_pitch_and_unaligned_views_use_the_scalar_path(cuda, port):
