@@ -21,7 +21,7 @@ NVCC = os.environ.get("EKAT_B200_NVCC", "nvcc")
 # sm_100a only (no PTX for other archs, no multi-arch fatbin). -lineinfo for ncu source pages.
 # No -use_fast_math / -fmad toggles: exactness is spelled with __d*_rn / __f*_rn intrinsics.
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-ccbin", "g++",
-         "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
+         "-Xcompiler", "-fPIC", "-Xptxas", "-v"] + os.environ.get("EKAT_B200_NVCC_FLAGS", "").split()  # (e.g. -DEKB_TRACE_BFB)
 
 
 def _stale(target, deps):

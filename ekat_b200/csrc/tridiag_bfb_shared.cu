@@ -30,6 +30,31 @@
 
 namespace ekb {
 
+// Phase trace for tuning, compiled in only with -DEKB_TRACE_BFB (tools/trace_bfb_shared.py builds that library for one run):
+// per traced CTA (blockIdx 0 and gridDim/2) and work item < 64, 16 counters in clock64 cycles, written by lane 0 of the
+// factor warp, forward warp 0, backward warp 0 and the three producers.
+#ifdef EKB_TRACE_BFB
+__device__ long long g_bfb_trace[2 * 64 * 16];
+__device__ __forceinline__ void bfb_trace_put(int it, int idx, long long v) {
+  const int cs = blockIdx.x == 0 ? 0 : (blockIdx.x == gridDim.x / 2 ? 1 : -1);
+  if (cs >= 0 && it < 64 && (threadIdx.x & 31) == 0) g_bfb_trace[(cs * 64 + it) * 16 + idx] = v;
+}
+#define TR_DECL(name) long long name = 0
+#define TR_WAIT(bar, par, acc)      \
+  {                                 \
+    const long long t_ = clock64(); \
+    mbar_wait(bar, par);            \
+    acc += clock64() - t_;          \
+  }
+#define TR_PUT(it, idx, v) bfb_trace_put(it, idx, v)
+#define TR_NOW() clock64()
+#else
+#define TR_DECL(name)
+#define TR_WAIT(bar, par, acc) mbar_wait(bar, par)
+#define TR_PUT(it, idx, v)
+#define TR_NOW() 0
+#endif
+
 template <typename R, int CPT>
 __global__ void __launch_bounds__(512, 1)
 k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
@@ -104,10 +129,13 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
       R yprev[CPT];
 #pragma unroll
       for (int j = 0; j < CPT; ++j) yprev[j] = (R)0;
+      TR_DECL(w_plx);
+      TR_DECL(w_ready);
+      if (jw == 0) TR_PUT(it, 4, TR_NOW());
       for (int k = 0; k < nch; ++k) {
         const int sl = slot(k, it), s = rs;
-        mbar_wait(&plxj[sl], (unsigned)(it & 1));
-        mbar_wait(&ready[s], rph);
+        TR_WAIT(&plxj[sl], (unsigned)(it & 1), w_plx);
+        TR_WAIT(&ready[s], rph, w_ready);
         ring_advance(NS);
         const V* rm = RING + (size_t)s * 2 * CH;
         V* px = PXj + (size_t)sl * CH;
@@ -131,6 +159,11 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         for (int u = 0; u < LB; ++u) px[u * 32 + lane] = x[u];
       }
       __syncwarp();
+      if (jw == 0) {
+        TR_PUT(it, 5, TR_NOW());
+        TR_PUT(it, 6, w_plx);
+        TR_PUT(it, 7, w_ready);
+      }
       if (lane == 0) mbar_arrive(&fdone[jw]);  // x' of this right-hand side (and, through `ready`, the pivots) are in place
     }
   } else if (warp < 2 * rh) {
@@ -155,13 +188,23 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
       auto refill = [&](int jb) {  // lane 0: the slot of this item's chunk nch-1-jb is free again: it is the next item's chunk jb
         if (has1) load_x(it + 1, jb, c0_n1, xrow_n1);
       };
-      mbar_wait(&fdone[jw], (unsigned)(it & 1));
+      TR_DECL(w_fdone);
+      TR_DECL(w_uraw);
+      TR_DECL(w_store);
+      TR_DECL(w_sec_a);
+      TR_DECL(w_sec_b);
+      TR_DECL(w_sec_c);
+      TR_WAIT(&fdone[jw], (unsigned)(it & 1), w_fdone);
+      if (jw == 0) TR_PUT(it, 8, TR_NOW());
       R xv[CPT];
 #pragma unroll
       for (int j = 0; j < CPT; ++j) xv[j] = (R)0;
       for (int jb = 0; jb < nch; ++jb) {
         const int k = nch - 1 - jb, sl = slot(k, it), s = rs;
-        mbar_wait(&uraw[s], rph);
+        TR_WAIT(&uraw[s], rph, w_uraw);
+#ifdef EKB_TRACE_BFB
+        const long long ta_ = clock64();
+#endif
         ring_advance(NU);
         const V* bu = URING + (size_t)s * CH;
         const V* pc = PD + (size_t)sl * CH;
@@ -178,6 +221,10 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
           mbar_arrive(&cfree[sl]);
           mbar_arrive(&ufree[s]);
         }
+#ifdef EKB_TRACE_BFB
+        const long long tb_ = clock64();
+        w_sec_a += tb_ - ta_;
+#endif
         if (k == nfull) {
           // partial top chunk (ntail levels): a tensor store would spill into the next right-hand side -> plain stores
           const int64_t col = (int64_t)c0 + lane * CPT;
@@ -232,18 +279,35 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
             for (int u = 0; u < LB; ++u) y[u] = ys[u];
             bfb_bwd_chunk<R, CPT, LB, true>(y, c, ui, xv, bad);
           }
+#ifdef EKB_TRACE_BFB
+          const long long tc_ = clock64();
+          w_sec_b += tc_ - tb_;
+#endif
 #pragma unroll
           for (int u = 0; u < LB; ++u) px[u * 32 + lane] = y[u];
           fence_proxy_async();  // generic-proxy writes of this chunk -> visible to the TMA store
           __syncwarp();
+#ifdef EKB_TRACE_BFB
+          w_sec_a += clock64() - tc_;  // (trace: STS + fence + syncwarp are booked on the load section's counter)
+#endif
           if (lane == 0) {
             tma_store_2d(&mx, c0, xrow0 + k * LB, PXj + (size_t)sl * CH);
             tma_store_commit();
             if (jb - jb0 >= kSD) {
+#ifdef EKB_TRACE_BFB
+              const long long t_ = clock64();
+#endif
               tma_store_wait_read<kSD>();  // the store committed kSD steps ago has read its slot
+#ifdef EKB_TRACE_BFB
+              w_store += clock64() - t_;
+#endif
               refill(jb - kSD);
             }
           }
+#ifdef EKB_TRACE_BFB
+          __syncwarp();
+          w_sec_c += clock64() - tc_;
+#endif
         }
       }
       if (lane == 0) {
@@ -251,6 +315,15 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         for (int jb = tmax(jb0, nch - kSD); jb < nch; ++jb) refill(jb);
       }
       __syncwarp();
+      if (jw == 0) {
+        TR_PUT(it, 9, TR_NOW());
+        TR_PUT(it, 10, w_fdone);
+        TR_PUT(it, 11, w_uraw);
+        TR_PUT(it, 12, w_store);
+        TR_PUT(it, 13, w_sec_a);
+        TR_PUT(it, 14, w_sec_b);
+        TR_PUT(it, 15, w_sec_c);
+      }
     }
   } else if (warp == 2 * rh) {
     // ================================================================ factor warp (:292-303)
@@ -261,11 +334,14 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         dprev[j] = (R)1;
         uprev[j] = (R)0;
       }
+      TR_DECL(w_raw);
+      TR_DECL(w_plc);
+      TR_PUT(it, 0, TR_NOW());
       for (int k = 0; k < nch; ++k) {
         const int sl = slot(k, it), s = rs;
-        mbar_wait(&raw[s], rph);
+        TR_WAIT(&raw[s], rph, w_raw);
         ring_advance(NS);
-        mbar_wait(&plc[sl], (unsigned)(it & 1));
+        TR_WAIT(&plc[sl], (unsigned)(it & 1), w_plc);
         V* r0 = RING + (size_t)s * 2 * CH;
         V* pc = PD + (size_t)sl * CH;
         V a[LB], b[LB], c[LB], om[LB], od[LB];
@@ -326,6 +402,9 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         __syncwarp();
         if (lane == 0) mbar_arrive(&ready[s]);
       }
+      TR_PUT(it, 1, TR_NOW());
+      TR_PUT(it, 2, w_raw);
+      TR_PUT(it, 3, w_plc);
     }
   } else if (warp == 2 * rh + 1) {
     // ================================================================ forward-ring producer
@@ -333,9 +412,10 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
       bool wrapped = false;
       for (int it = 0; it < nit; ++it) {
         const int c0 = item_c0(it);
+        TR_DECL(w_freeb);
         for (int k = 0; k < nch; ++k) {
           const int s = rs;
-          if (wrapped) mbar_wait(&freeb[s], rph ^ 1u);  // the use one lap earlier has been read by every forward warp
+          if (wrapped) TR_WAIT(&freeb[s], rph ^ 1u, w_freeb);  // the use one lap earlier has been read by every forward warp
           ring_advance(NS);
           if (rs == 0) wrapped = true;
           V* st = RING + (size_t)s * 2 * CH;
@@ -370,11 +450,13 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         tma_load_2d(PD + (size_t)sl * CH, &md, item_c0(it2), k * LB, &plc[sl]);
       };
       for (int k = 0; k < nch; ++k) load_c(0, k);
-      for (int it = 0; it + 1 < nit; ++it)
+      for (int it = 0; it + 1 < nit; ++it) {
+        TR_DECL(w_cfree);
         for (int jb = 0; jb < nch; ++jb) {  // the slot of this item's chunk nch-1-jb becomes the next item's chunk jb
-          mbar_wait(&cfree[slot(nch - 1 - jb, it)], (unsigned)(it & 1));
+          TR_WAIT(&cfree[slot(nch - 1 - jb, it)], (unsigned)(it & 1), w_cfree);
           load_c(it + 1, jb);
         }
+      }
     }
   }
 }
@@ -435,6 +517,13 @@ int tridiag_bfb_shared(R* dl, R* d, R* du, R* X, const R* Xin, int64_t ncol, int
   note_launch(sizeof(R) == 8 ? "tridiag_bfb_shared<f64>" : "tridiag_bfb_shared<f32>");
   return check_cuda(cudaGetLastError());
 }
+
+#ifdef EKB_TRACE_BFB
+extern "C" int ekat_b200_debug_trace_bfb(long long* out, int n) {
+  if (n > 2 * 64 * 16) n = 2 * 64 * 16;
+  return check_cuda(cudaMemcpyFromSymbol(out, g_bfb_trace, (size_t)n * sizeof(long long)));
+}
+#endif
 
 template int tridiag_bfb_shared<double>(double*, double*, double*, double*, const double*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
 template int tridiag_bfb_shared<float>(float*, float*, float*, float*, const float*, int64_t, int, int, int64_t, int64_t, cudaStream_t);
