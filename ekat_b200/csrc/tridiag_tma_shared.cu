@@ -648,7 +648,7 @@ static int run_shared(bool exact, R* dl, R* d, R* du, R* X, const R* Xin, int64_
     for (int cand = tmin(nrhs, 13); cand >= 1; --cand) {
       if (nrhs % cand) continue;
       if (tu.cols_per_cta > 0 && cand != tu.cols_per_cta) continue;  // tuning override: right-hand sides per CTA
-      int n = 8;
+      int n = tu.prefetch > 8 ? tmin(tu.prefetch, 16) : 8;
       while (n >= want && smem_for(cand, n) > kMaxSmemPerCta) --n;
       if (n >= want) {
         rh = cand;
@@ -665,6 +665,17 @@ static int run_shared(bool exact, R* dl, R* d, R* du, R* X, const R* Xin, int64_
     return exact ? shared_ctas_per_sm<R, true, CM>(shared_threads(rh, cio), sm) : shared_ctas_per_sm<R, false, CM>(shared_threads(rh, cio), sm);
   };
   int per_sm = ctas(io, smem);
+  // A deeper ring where it costs no residency: the factor warp's lead over the copies is what the ring buys, and at the
+  // bench's shape 10 stages against 8 are worth 2 % (tools/sweep.py ring: 2 / 4 / 6 / 8 / 10 / 12 stages = 0.72 / 0.79 /
+  // 0.86 / 0.897 / 0.915 / 0.903 of the HBM peak; 14 stages lose the second CTA of an SM: 0.60)
+  if (tu.prefetch < 2 && ns == 8) {
+    for (int n2 = 10; n2 > ns; --n2)
+      if (smem_for(rh, n2) <= kMaxSmemPerCta && ctas(io, smem_for(rh, n2)) >= per_sm) {
+        ns = n2;
+        smem = smem_for(rh, ns);
+        break;
+      }
+  }
   // Small batches (BASELINE config 1: 21,600 columns x 72 levels = 675 tiles for 148 SMs) are latency-bound: what a
   // launch costs is the number of WAVES of tiles, each a full forward + backward dependent chain, not bytes. There
   // the deep ring and the io warps are traded for residency: fewer ring stages (less shared memory) and no io warps

@@ -182,6 +182,17 @@ if __name__ == "__main__":
             tridiag_case(s, "f32", 345600, 128)
             tridiag_case(s, "f64", 3145728, 128)
             tridiag_case(s, "f64", 21600, 72)
+    if "ring" in what:  # the bench's dominant kernel: ring stages 2..8 (fewer stages = less shared memory = a third CTA per SM), io warps off
+        tridiag_case("thomas", "f64", 3145728, 128, tunings=[(0, p, 0) for p in (0, 2, 4, 6, 8, 9, 10, 11, 12, 14, 16)] + [(0, 0, 8)])
+        tridiag_case("thomas", "f64", 345600, 128, tunings=[(0, p, 0) for p in (0, 8, 10, 11, 12, 16)])
+        tridiag_case("thomas", "f32", 3145728, 128, tunings=[(0, p, 0) for p in (0, 8, 10, 12, 16)])
+        tridiag_case("thomas", "f64", 1572864, 128, nrhs=10, tunings=[(0, p, 0) for p in (0, 8, 10, 12)])
+    if "bfbring" in what:  # bfb_stream: ring stages against tiles per SM
+        tridiag_case("bfb", "f64", 3145728, 128, tunings=[(c, 0, 0) for c in (0, 2, 3, 4, 5, 6)] + [(0, p, 0) for p in (2, 6, 8)])
+        tridiag_case("thomas", "f64", 3145728, 128)
+        tridiag_case("thomas", "f64", 345600, 128)
+        tridiag_case("thomas", "f64", 345600, 72)
+        tridiag_case("thomas", "f64", 21600, 72)
     if "split" in what:  # one right-hand side: warp-specialised kernel (default for thomas) against the one-warp kernel (variant 4)
         for s in ("bfb", "thomas"):
             for dt in ("f64", "f32"):
