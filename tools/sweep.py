@@ -193,6 +193,10 @@ if __name__ == "__main__":
         tridiag_case("thomas", "f64", 345600, 128)
         tridiag_case("thomas", "f64", 345600, 72)
         tridiag_case("thomas", "f64", 21600, 72)
+    if "f32split" in what:  # f32, one right-hand side: one-warp-per-tile kernel (default) against the warp-specialised one (variant 9)
+        for ncol in (3145728, 345600):
+            tridiag_case("thomas", "f32", ncol, 128, tunings=[(0, 0, 0), (0, 0, 9), (0, 8, 9), (0, 12, 9), (0, 16, 9)])
+            tridiag_case("bfb", "f32", ncol, 128, tunings=[(0, 0, 0), (0, 0, 9)])
     if "split" in what:  # one right-hand side: warp-specialised kernel (default for thomas) against the one-warp kernel (variant 4)
         for s in ("bfb", "thomas"):
             for dt in ("f64", "f32"):
