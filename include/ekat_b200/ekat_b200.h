@@ -405,7 +405,12 @@ int ekat_b200_lin_interp_host_f32(ekat_b200_pipeline* p, const float* x1, const 
 /* Self test of the bit-exact division used by bfb / cr / LinInterp (the IEEE divide with its reciprocal
  * hoisted off the dependent chain, csrc/common.cuh) against the compiler's __ddiv_rn / __fdiv_rn on n random
  * operand pairs: mode 0 = random bit patterns (all exponents, denormals, infinities), mode 1 = well-scaled
- * operands. *mismatches (device uint64) += number of bitwise differences; 0 is the only acceptable answer. */
+ * operands. *mismatches (device uint64) += number of bitwise differences; 0 is the only acceptable answer.
+ * Modes 2 / 3: the same two populations through the CERTIFIED quotient of the bfb factorisation (reciprocal taken
+ * of a predicted pivot up to 2^-22 off, quotient accepted only with its exact remainder below half an ulp): counts
+ * quotients that passed the certificate and differ from __ddiv_rn / __fdiv_rn -- again 0 is the only acceptable
+ * answer. Modes 4 / 5 (and 6 / 7 with a 2^-52 prediction error) count how often the certificate sends a quotient
+ * to the full-range division instead (a rate, not an error). */
 int ekat_b200_selftest_div_f64(uint64_t n, uint64_t seed, int mode, uint64_t* mismatches, ekat_b200_stream_t s);
 int ekat_b200_selftest_div_f32(uint64_t n, uint64_t seed, int mode, uint64_t* mismatches, ekat_b200_stream_t s);
 
