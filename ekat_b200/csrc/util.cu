@@ -285,15 +285,15 @@ __global__ void k_selftest_div(uint64_t n, uint64_t seed, int mode, unsigned lon
       const uint64_t rp = splitmix64(seed ^ (0x9e3779b97f4a7c15ull * (i + 1)));
       const int sh = mode >= 6 ? 1 : (int)(rp & 31);  // perturbation 2^-53 .. 2^-22 relative (modes 6, 7: 2^-52, flag counts)
       const R bp = b * ((R)1 + (R)((rp >> 8 & 1) ? 1 : -1) * (R)ldexp(1.0, -(sizeof(R) == 8 ? 53 : 24) + (sizeof(R) == 8 ? sh : sh % 12)));
-      for (int z = 0; z < 2; ++z) {
-        const R an = z ? (R)0 : a;
+      for (int z = 0; z < 3; ++z) {
+        const R an = z == 0 ? a : (z == 1 ? (R)0 : -(R)0);  // also +0 and -0 numerators (the sign of a zero quotient)
         const R r = rcp_seed(bp);
         const R q0 = x_mul(an, r);
         const R m = fma(r, fma(-b, q0, an), q0);
         bool flagged = false;
         certify_quotient(an, b, m, flagged);
         const R ws = DivRef<R>::ref(an, b);
-        if (mode >= 4) bad += flagged ? 1 : 0;
+        if (mode >= 4) bad += (flagged && z < 2) ? 1 : 0;  // (-0 numerators are always sent to the full-range division: not counted)
         else if (!flagged && DivRef<R>::bits(m) != DivRef<R>::bits(ws) && !(m != m && ws != ws)) ++bad;
       }
       continue;

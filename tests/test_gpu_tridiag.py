@@ -187,6 +187,41 @@ def test_tuning_variants_agree(cuda, port):
 
 
 @pytest.mark.parametrize("dt", ["f64", "f32"])
+@pytest.mark.parametrize("solver", ["bfb", "cr"])
+def test_signed_zeros_bit_exact(cuda, port, dt, solver):
+    """+0 / -0 sub- and super-diagonal entries and right-hand sides: the quotients 0/d' and the products m*0 carry the
+    sign of the zero, and the speculative divisions must hand every case their fast path is not proven for (a -0
+    numerator ends on it with the wrong zero) to the full-range division. Bit for bit on every route, also the
+    multipliers and pivots written back under CLOBBER_DIAGS."""
+    npdt, _ = DT[dt]
+    rng = np.random.default_rng(5)
+    for layout, nrow, nrhs, nA, ncol, clobber in [(ekat_b200.LEV_MAJOR, 128, 1, 1, 5000, False), (ekat_b200.LEV_MAJOR, 72, 1, 1, 700, False),
+                                                  (ekat_b200.LEV_MAJOR, 128, 10, 1, 4800, False), (ekat_b200.LEV_MAJOR, 72, 10, 1, 4800, False),
+                                                  (ekat_b200.LEV_MAJOR, 128, 4, 4, 2000, True), (ekat_b200.COL_MAJOR, 128, 1, 1, 3000, False),
+                                                  (ekat_b200.COL_MAJOR, 128, 10, 1, 2048, False), (ekat_b200.COL_MAJOR, 64, 2, 2, 999, True)]:
+        if solver == "cr" and (clobber or nA > 1):
+            continue
+        A, B = port.fill_tridiag(npdt, ncol, nrow, nA, nrhs, col0=9)
+        for arr, k in ((A[:, 0], 0.15), (A[:, 2], 0.15), (B, 0.2)):  # dl, du, right-hand sides
+            m = rng.random(arr.shape)
+            arr[m < k / 2] = 0.0
+            arr[(m >= k / 2) & (m < k)] = -0.0
+        B[1] = -0.0  # a whole column of -0 right-hand sides, one of +0
+        B[2] = 0.0
+        Aref, Xref = A.copy(), B.copy()
+        port.tridiag(REFNAME[solver], Aref, Xref)
+        got, Aout = run_gpu(solver, A, B, layout, cuda, clobber=clobber, pad=(-ncol) % 4 if layout == ekat_b200.LEV_MAJOR else 0)
+        assert bits_equal(got, Xref), (solver, dt, layout, nrow, nrhs, nA, lib_last())
+        if clobber:
+            assert bits_equal(Aout[:, 0, 1:], Aref[:, 0, 1:]) and bits_equal(Aout[:, 1], Aref[:, 1]), (solver, dt, layout, nrow)
+
+
+def lib_last():
+    from ekat_b200._lib import lib
+    return lib().ekat_b200_last_kernel().decode()
+
+
+@pytest.mark.parametrize("dt", ["f64", "f32"])
 def test_pipelined_division_is_ieee(cuda, dt):
     """The divide used on the exact paths (reciprocal hoisted off the chain) equals __ddiv_rn / __fdiv_rn bit for
     bit on 2^28 random bit patterns (all exponents, denormals, infinities) and 2^28 well-scaled operands."""
