@@ -262,16 +262,22 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
           for (int j = 0; j < CPT; ++j) sxv[j] = xv[j];
 #pragma unroll
           for (int u = 0; u < LB; ++u) ys[u] = y[u];
-          bool bad = false;
+          unsigned badu = 0;  // the pivots are validated once per chunk, off the chain; a level checks numerator and quotient only
+#pragma unroll
+          for (int u = 0; u < LB; ++u) {
+#pragma unroll
+            for (int j = 0; j < CPT; ++j) badu |= divisor_in_range(c[u].v[j]) ? 0u : 1u;
+          }
 #pragma unroll
           for (int u = LB - 1; u >= 0; --u) {
 #pragma unroll
             for (int j = 0; j < CPT; ++j) {
               const R num = x_sub(y[u].v[j], x_mul(ui[u].v[j], xv[j]));  // X(i-1) - du(i-1)*X(i)   :318-319
-              xv[j] = div_spec(num, c[u].v[j], rr[u].v[j], bad);
+              xv[j] = div_spec_b(num, c[u].v[j], rr[u].v[j], badu);
               y[u].v[j] = xv[j];
             }
           }
+          bool bad = badu != 0;
           if (__any_sync(0xffffffffu, bad)) {  // rare operands somewhere in the warp: redo with the full-range division
 #pragma unroll
             for (int j = 0; j < CPT; ++j) xv[j] = sxv[j];
