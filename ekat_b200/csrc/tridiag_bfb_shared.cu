@@ -381,7 +381,7 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
                 dc = x_sub(b[u].v[j], x_mul(m, uprev[j]));         // d(i) -= dl(i)*du(i-1)   :301
               } else {
                 dc = dprev[j];
-                m = bfb_pivot_step(av, b[u].v[j], uprev[j], dc, rp[j], bad);
+                m = bfb_factor_level(av, b[u].v[j], uprev[j], dc, rp[j], bad);
               }
               om[u].v[j] = m;
               od[u].v[j] = dc;

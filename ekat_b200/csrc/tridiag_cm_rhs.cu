@@ -107,7 +107,7 @@ k_tridiag_cm_rhs(const CmArgs a) {
           for (int u = 0; u < kCmLB; ++u) {
             bool f = false;
             R dn = dprev, rn = rp;
-            const R m = bfb_pivot_step(va[u], vb[u], uprev, dn, rn, f);
+            const R m = bfb_factor_level(va[u], vb[u], uprev, dn, rn, f);
             bad = bad || (f && i0 + u > 0 && u < n);
             if (i0 + u > 0) {
               dprev = dn;

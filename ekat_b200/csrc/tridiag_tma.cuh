@@ -101,7 +101,7 @@ __device__ __forceinline__ void bfb_fwd_chunk(const Vec<R, CPT> (&a)[LB], const 
         dc = x_sub(b[u].v[j], x_mul(m, uprev[j]));        // d(i) -= dl(i)*du(i-1)      :301
       } else {
         dc = dprev[j];
-        m = bfb_pivot_step(av, b[u].v[j], uprev[j], dc, rp[j], bad);
+        m = bfb_factor_level(av, b[u].v[j], uprev[j], dc, rp[j], bad);
       }
       const R xc = x_sub(x[u].v[j], x_mul(m, xprev[j]));  // X(i) -= dl(i)*X(i-1)       :315-316
       o0[u].v[j] = dc;
@@ -135,7 +135,7 @@ __device__ __forceinline__ void bfb_fwd_chunk_m(const Vec<R, CPT> (&a)[LB], cons
         dc = x_sub(b[u].v[j], x_mul(m, uprev[j]));
       } else {
         dc = dprev[j];
-        m = bfb_pivot_step(av, b[u].v[j], uprev[j], dc, rp[j], bad);
+        m = bfb_factor_level(av, b[u].v[j], uprev[j], dc, rp[j], bad);
       }
       om[u].v[j] = (u == 0 && first) ? a[u].v[j] : m;
       const R xc = x_sub(x[u].v[j], x_mul(m, xprev[j]));

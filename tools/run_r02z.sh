@@ -2,7 +2,7 @@
 # reference arm), launch list. Every ncu command runs only after the same program has exited 0 without ncu.
 set -x
 cd $GRAFT_REPO_ROOT
-TAG=r02z
+TAG=r02zf
 timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print(\"smoke ok\")" > gpurun_out/${TAG}_smoke.txt 2>&1; tail -2 gpurun_out/${TAG}_smoke.txt
 timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest_gpu.log 2>&1; tail -3 gpurun_out/${TAG}_pytest_gpu.log
 CMD="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu --no-extras --no-strong"
