@@ -53,6 +53,28 @@ def timeit(fn, restore=None, iters=10, flush=False):
     return tot / iters
 
 
+def time_graph(fn, n=50, reps=5):
+    """Warm (L2-resident) timing as bench.py's small rows: n back-to-back launches in a CUDA graph, ms per launch."""
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=st):
+            for _ in range(n):
+                fn()
+        best = 1e9
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            g.replay()
+            b.record()
+            torch.cuda.synchronize()
+            best = min(best, a.elapsed_time(b) / n)
+    return best
+
+
 def report(**kw):
     print(json.dumps(kw), flush=True)
 
@@ -197,6 +219,17 @@ if __name__ == "__main__":
         for ncol in (3145728, 345600):
             tridiag_case("thomas", "f32", ncol, 128, tunings=[(0, 0, 0), (0, 0, 9), (0, 8, 9), (0, 12, 9), (0, 16, 9)])
             tridiag_case("bfb", "f32", ncol, 128, tunings=[(0, 0, 0), (0, 0, 9)])
+    if "li21k" in what:  # BASELINE config 2 at its stated 21,600 columns, warm: columns per tile
+        for N in (1, 16):
+            x1, y1, x2 = li_fill(torch.float64, 21600, 72, 128, N, device=dev)
+            li = LinInterp(21600, 72, 128, torch.float64, N, device=dev)
+            y2 = torch.zeros((21600, li.pitch2), dtype=torch.float64, device=dev)
+            alg = (72 + 128) * 2 * 8 * 21600
+            for tu in [(c, 0, v) for v in (0, 21, 22) for c in (0, 4, 8, 12, 16, 24, 32)]:
+                lib().ekat_b200_set_tuning(*tu)
+                ms = time_graph(lambda: li.run(x1, x2, y1, y2))
+                lib().ekat_b200_set_tuning(0, 0, 0)
+                report(kernel="lin_interp warm", pack=N, tuning=tu, us=round(ms * 1e3, 2), frac=round(alg / ms / 1e6 / PEAK, 3))
     if "split" in what:  # one right-hand side: warp-specialised kernel (default for thomas) against the one-warp kernel (variant 4)
         for s in ("bfb", "thomas"):
             for dt in ("f64", "f32"):
