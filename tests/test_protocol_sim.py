@@ -11,3 +11,21 @@ import sim_shared_protocol as sim  # noqa: E402
 def test_shared_kernel_protocol_random_schedules():
     for seed in (1, 2, 3):
         assert sim.main(trials=150, seed=seed) == 150
+
+
+def test_bfb_shared_kernel_protocol_random_schedules():
+    """The same for k_tridiag_bfb_shared (csrc/tridiag_bfb_shared.cu): forward / backward / factor warps and three producer
+    threads over two rings and mirrored plane slots, 1..7 items per CTA, ragged top chunks."""
+    import sim_bfb_shared_protocol as simb
+    for seed in (1, 2):
+        assert simb.main(trials=120, seed=seed) == 120
+
+
+def test_bfb_shared_protocol_model_notices_broken_protocols():
+    """The model is only worth something if it fails on a wrong protocol: a refill that does not wait for the tensor store
+    to have read its slot, a ring producer and a plane producer that do not wait for their consumers."""
+    import pytest
+    import sim_bfb_shared_protocol as simb
+    for broken in ("refill_without_wait", "ring_without_wait", "plane_without_wait"):
+        with pytest.raises(AssertionError):
+            simb.main(trials=200, seed=3, break_it=broken)
