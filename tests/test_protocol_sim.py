@@ -29,3 +29,16 @@ def test_bfb_shared_protocol_model_notices_broken_protocols():
     for broken in ("refill_without_wait", "ring_without_wait", "plane_without_wait"):
         with pytest.raises(AssertionError):
             simb.main(trials=200, seed=3, break_it=broken)
+
+
+def test_bfb_stream_kernel_protocol_random_schedules():
+    """k_tridiag_bfb_stream (csrc/tridiag_bfb_stream.cu), two sweeping warps: io thread, input ring, two output buffers, the
+    read-back of x' after the forward stores have completed, the named-barrier pair of the chain hand-over -- and the model
+    fails on a read-back that does not wait for the stores and on an output buffer freed before its store has read it."""
+    import pytest
+    import sim_bfb_stream_protocol as sims
+    for seed in (1, 2):
+        assert sims.main(trials=150, seed=seed) == 150
+    for broken in ("readback_without_flush", "ob_free_without_wait"):
+        with pytest.raises(AssertionError):
+            sims.main(trials=300, seed=3, break_it=broken)
