@@ -42,3 +42,16 @@ def test_bfb_stream_kernel_protocol_random_schedules():
     for broken in ("readback_without_flush", "ob_free_without_wait"):
         with pytest.raises(AssertionError):
             sims.main(trials=300, seed=3, break_it=broken)
+
+
+def test_fused_kernel_protocol_random_schedules():
+    """k_solve_remap_roles (csrc/fused_tma.cu, config 4 in one kernel): planes handed from tile to tile by the last remap
+    warp out (atomic counters) and by the factor warp once every solver warp has arrived -- and the model fails when the
+    factor warp does not wait for the solvers or when the FIRST warp out requests the next tile's plane."""
+    import pytest
+    import sim_fused_protocol as simf
+    for seed in (1, 2):
+        assert simf.main(trials=150, seed=seed) == 150
+    for broken in ("factor_without_abar", "first_one_out"):
+        with pytest.raises(AssertionError):
+            simf.main(trials=300, seed=3, break_it=broken)
