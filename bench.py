@@ -591,14 +591,20 @@ def run_extras(torch, dev, peak):
         torch.cuda.synchronize()
         return (time.perf_counter() - t0) / n * 1e6
 
-    def replay(fn, n=50, cold=False):
+    def replay(fn, n=50, cold=False, restore=None):
         """Kernel duration of a small case: n launches captured in a CUDA graph and replayed between ONE event pair
         (launch gaps between consecutive kernels included, no host launch path, no per-event overhead -- an event
         pair around a single near-empty kernel reads ~6.5 us on this box, more than these kernels take). The solvers
-        run in place, so launch i solves the solution of launch i-1 again: same work, no restore inside the graph.
+        run in place, so launch i solves the solution of launch i-1 again: same work, no restore inside the graph;
+        `restore` puts the right-hand sides back before the warm-up and again before the timed replay, so that the timed
+        launches are solves 1..n of fresh data (a hundred solves on end shrink the values towards the range where the
+        bit-exact solvers leave their fast division path: that would be timed, too).
         cold: a 512 MB fill between the launches (outside the kernel's own time it is subtracted as measured)."""
         st = torch.cuda.Stream()
         g = torch.cuda.CUDAGraph()
+        if restore:
+            restore()
+            torch.cuda.synchronize()
         with torch.cuda.stream(st):
             fn()
             torch.cuda.synchronize()
@@ -609,6 +615,9 @@ def run_extras(torch, dev, peak):
                     fn()
         g.replay()
         torch.cuda.synchronize()
+        if restore:
+            restore()
+            torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         g.replay()
@@ -653,9 +662,9 @@ def run_extras(torch, dev, peak):
         alg = (3 * nA + 2 * nrhs) * nlev * w * ncol
         kw = {}
         if small and not clobber:
-            ms = replay(fn)
+            ms = replay(fn, restore=restore)
             kw["timing"] = "graph replay of 50 back-to-back launches"
-            kw["cold_ms"] = replay(fn, cold=True)
+            kw["cold_ms"] = replay(fn, cold=True, restore=restore)
             kw["cold_frac"] = alg / kw["cold_ms"] / 1e6 / peak
             kw["wall_us"] = wall(fn)
             kw["single_launch_event_pair_ms"] = timed(fn, restore=restore)
@@ -792,7 +801,7 @@ def rows_round2(torch, dev, peak, timed, wall, row, replay):
         alg = 4 * nlev * 8 * ncol
         for fn, nm, words in ((fused, "fused (one kernel, diagonals never in HBM)", 4), (two_pass, "two passes (diffusion_matrix + thomas)", 10)):
             if small:
-                ms = replay(fn)
+                ms = replay(fn, restore=lambda: X.copy_(B))
                 kw = {"timing": "graph replay of 50 back-to-back launches"}
             else:
                 ms = timed(fn, restore=lambda: X.copy_(B))

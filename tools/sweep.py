@@ -53,8 +53,10 @@ def timeit(fn, restore=None, iters=10, flush=False):
     return tot / iters
 
 
-def time_graph(fn, n=50, reps=5):
-    """Warm (L2-resident) timing as bench.py's small rows: n back-to-back launches in a CUDA graph, ms per launch."""
+def time_graph(fn, n=50, reps=5, restore=None):
+    """Warm (L2-resident) timing as bench.py's small rows: n back-to-back launches in a CUDA graph, ms per launch.
+    restore: put in-place operands back before every timed replay (solving a solution again and again shrinks the values
+    until the bit-exact solvers leave their fast division path -- the first version of the c1bfb sweep measured that)."""
     st = torch.cuda.Stream()
     with torch.cuda.stream(st):
         for _ in range(3):
@@ -66,6 +68,9 @@ def time_graph(fn, n=50, reps=5):
                 fn()
         best = 1e9
         for _ in range(reps):
+            if restore:
+                restore()
+                torch.cuda.synchronize()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             g.replay()
@@ -230,6 +235,19 @@ if __name__ == "__main__":
                 ms = time_graph(lambda: li.run(x1, x2, y1, y2))
                 lib().ekat_b200_set_tuning(0, 0, 0)
                 report(kernel="lin_interp warm", pack=N, tuning=tu, us=round(ms * 1e3, 2), frac=round(alg / ms / 1e6 / PEAK, 3))
+    if "c1bfb" in what:  # BASELINE config 1, bfb, warm: ring stages, plane prefetch distance, sweeping-warp forms, other kernels
+        dl, d, du, B = T.fill(torch.float64, 21600, 72, 1, 1, device=dev)
+        X = B.clone()
+        alg = 5 * 72 * 8 * 21600
+        for tu in [(0, 0, 0)] + [(c, p, v) for v in (0, 5, 11) for c in (0, 2, 3, 4) for p in (0, 2, 5, 9)] + [(0, 0, 4), (0, 0, 6), (0, 0, 9), (0, 0, 10)]:
+            lib().ekat_b200_set_tuning(*tu)
+            try:
+                ms = time_graph(lambda: T.bfb(dl, d, du, X), restore=lambda: X.copy_(B))
+                name = lib().ekat_b200_last_kernel().decode()
+            except Exception as e:  # a pinned form may not support the shape
+                ms, name = float("nan"), str(e)[:40]
+            lib().ekat_b200_set_tuning(0, 0, 0)
+            report(kernel=name, tuning=tu, us=round(ms * 1e3, 2), frac=round(alg / ms / 1e6 / PEAK, 3))
     if "split" in what:  # one right-hand side: warp-specialised kernel (default for thomas) against the one-warp kernel (variant 4)
         for s in ("bfb", "thomas"):
             for dt in ("f64", "f32"):
