@@ -55,7 +55,9 @@ __device__ __forceinline__ void bfb_trace_put(int it, int idx, long long v) {
 #define TR_NOW() 0
 #endif
 
-template <typename R, int CPT>
+// RAGGED: the level count is not a multiple of the chunk (the top chunk then leaves by plain stores); the instantiation
+// without it carries none of that in the way-back loop, the warp whose instruction stream bounds the kernel
+template <typename R, int CPT, bool RAGGED>
 __global__ void __launch_bounds__(512, 1)
 k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_constant__ CUtensorMap md,
                      const __grid_constant__ CUtensorMap mdu, const __grid_constant__ CUtensorMap mx,
@@ -66,7 +68,7 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
   constexpr unsigned CHUNK_BYTES = LB * W * sizeof(R);
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int nfull = nlev / LB, ntail = nlev - nfull * LB, nch = nfull + (ntail ? 1 : 0), nslot = nch;
+  const int nfull = nlev / LB, ntail = RAGGED ? nlev - nfull * LB : 0, nch = nfull + (RAGGED ? 1 : 0), nslot = nch;
 
   uint64_t* raw = reinterpret_cast<uint64_t*>(smem_raw);  // [NS]  dl | du of a chunk landed in a forward-ring stage
   uint64_t* ready = raw + NS;                             // [NS]  the factor warp turned dl into multipliers there
@@ -118,7 +120,7 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
   const uint64_t pol_stream = l2_policy_evict_first();
   // a slot is refilled kSD steps after its tensor store was committed (wait_group.read<kSD>); 1 / 2 / 3: 4.15 / 4.09 / 4.08 TB/s
   constexpr int kSD = 1;
-  const int jb0 = ntail ? 1 : 0;  // the partial top chunk (way-back step 0) leaves by plain stores
+  constexpr int jb0 = RAGGED ? 1 : 0;  // the partial top chunk (way-back step 0) leaves by plain stores
 
   if (warp < rh) {
     // ================================================================ forward warp of right-hand side `warp`
@@ -225,7 +227,7 @@ k_tridiag_bfb_shared(const __grid_constant__ CUtensorMap mdl, const __grid_const
         const long long tb_ = clock64();
         w_sec_a += tb_ - ta_;
 #endif
-        if (k == nfull) {
+        if (RAGGED && k == nfull) {
           // partial top chunk (ntail levels): a tensor store would spill into the next right-hand side -> plain stores
           const int64_t col = (int64_t)c0 + lane * CPT;
 #pragma unroll
@@ -516,7 +518,7 @@ int tridiag_bfb_shared(R* dl, R* d, R* du, R* X, const R* Xin, int64_t ncol, int
   const int64_t ntiles = (ncol + W - 1) / W, nwork = ntiles * ngroups;
   if (nwork >= (int64_t)1 << 30) return EKAT_B200_ERR_UNSUPPORTED;
   const int64_t grid = tmin<int64_t>(nwork, (int64_t)kNumSms);
-  auto k = k_tridiag_bfb_shared<R, CPT>;
+  auto k = (nlev % kLB) ? k_tridiag_bfb_shared<R, CPT, true> : k_tridiag_bfb_shared<R, CPT, false>;
   const int rc = allow_smem(k, smem);
   if (rc) return rc;
   k<<<(unsigned)grid, 32 * (2 * rh + 4), smem, stream>>>(mdl, md, mdu, mx, mxin, X, ncol, nlev, x_stride, rh, ngroups, (int)nwork, ns, nu);
